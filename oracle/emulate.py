@@ -1,0 +1,83 @@
+"""Operand-rounding emulation of the CUDA bf16 pipeline (TEST INFRASTRUCTURE).
+
+Restates what the sm_100a kernels compute, on CPU, so GPU results can be compared
+layer by layer far below the end-to-end tolerance: conv operands (activations after
+leaky-relu, and weights) rounded to bf16, products accumulated in fp32 (here fp64 then
+cast), bias / residual / MRF average in fp32.  Also used to pick which tensors may be
+stored in bf16 without breaking the 40 dB gate (numerics section).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from .hifigan_oracle import V1_CONFIG, LRELU_SLOPE, fold_weight_norm, get_padding
+
+
+def _r(x, mode):
+    if mode == "bf16":
+        return x.to(torch.bfloat16).to(x.dtype)
+    if mode == "tf32":
+        # round-to-nearest-even to 10 mantissa bits
+        i = x.float().view(torch.int32)
+        i = (i + 0x0FFF + ((i >> 13) & 1)) & ~0x1FFF
+        return i.view(torch.float32).to(x.dtype)
+    return x
+
+
+def generator_forward_emulated(sd, mel, cfg=V1_CONFIG, mode="bf16", residual="fp32",
+                               acc_dtype=torch.float64, taps=None):
+    """Same dataflow as oracle.generator_forward with operand rounding ``mode``.
+
+    residual: "fp32" keeps the residual stream x in fp32 between conv pairs,
+              "bf16" rounds it after every pair (what a bf16 residual buffer would do).
+    """
+    sd = fold_weight_norm(sd)
+    W = {k: (_r(v.float(), mode) if k.endswith("weight") else v.float()).to(acc_dtype)
+         for k, v in sd.items()}
+    nk = len(cfg["resblock_kernel_sizes"])
+    f32 = lambda t: t.float().to(acc_dtype)      # fp32 storage of an fp32-accumulated value
+
+    def conv(x, name, **kw):
+        return f32(F.conv1d(_r(x, mode), W[name + ".weight"], W[name + ".bias"], **kw))
+
+    with torch.no_grad():
+        x = conv(mel.to(acc_dtype), "conv_pre", padding=3)
+        if taps is not None:
+            taps["conv_pre"] = x.float()
+        for i, (u, k) in enumerate(zip(cfg["upsample_rates"], cfg["upsample_kernel_sizes"])):
+            x = F.leaky_relu(x, LRELU_SLOPE)
+            x = f32(F.conv_transpose1d(_r(x, mode), W[f"ups.{i}.weight"], W[f"ups.{i}.bias"],
+                                       stride=u, padding=(k - u) // 2))
+            if taps is not None:
+                taps[f"ups.{i}"] = x.float()
+            xs = None
+            for j, (rk, rd) in enumerate(zip(cfg["resblock_kernel_sizes"],
+                                             cfg["resblock_dilation_sizes"])):
+                p = f"resblocks.{i * nk + j}"
+                r = x
+                for m, d in enumerate(rd):
+                    xt = conv(F.leaky_relu(r, LRELU_SLOPE), f"{p}.convs1.{m}",
+                              padding=get_padding(rk, d), dilation=d)
+                    xt = conv(F.leaky_relu(xt, LRELU_SLOPE), f"{p}.convs2.{m}",
+                              padding=get_padding(rk, 1))
+                    r = f32(xt + r)
+                    if residual == "bf16" and m < 2:
+                        r = _r(r, "bf16")
+                if taps is not None:
+                    taps[p] = r.float()
+                xs = r if xs is None else f32(xs + r)
+            x = f32(xs / nk)
+            if taps is not None:
+                taps[f"mrf.{i}"] = x.float()
+        x = F.leaky_relu(x)
+        x = conv(x, "conv_post", padding=3)
+        x = torch.tanh(x)
+    return x.float()
+
+
+def snr_db(ref: torch.Tensor, got: torch.Tensor) -> float:
+    """Total-power SNR, 10 log10(sum ref^2 / sum err^2) (hard parts)."""
+    ref = ref.double()
+    err = got.double() - ref
+    return float(10 * torch.log10(ref.pow(2).sum() / err.pow(2).sum().clamp_min(1e-300)))

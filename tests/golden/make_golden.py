@@ -1,0 +1,143 @@
+"""Generate tests/golden/*.npz by running the REFERENCE's own modules (build container only).
+
+    python tests/golden/make_golden.py          # needs /root/reference (read-only)
+
+The reference has no tests or golden vectors for this path, so these
+fixtures are what pins the oracle: inputs are seeded here, outputs come from the imported
+reference classes (hifigan.Generator, model.modules.LengthRegulator, utils.tools.*,
+utils.model.vocoder_infer).  Weights are NOT stored (55 MB): they are regenerated from a
+seed by visual_onoma_to_wave_b200.synthetic.seeded_state_dict and checked by sha256.
+"""
+import hashlib
+import json
+import os
+import sys
+from unittest.mock import MagicMock
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+sys.path.insert(0, ROOT)
+
+from visual_onoma_to_wave_b200.synthetic import seeded_state_dict, synthetic_mel  # noqa: E402
+
+
+def import_reference():
+    """cwd-relative paths + stub the missing plotting/audio deps."""
+    for m in ("matplotlib", "matplotlib.pyplot", "librosa", "librosa.util", "librosa.filters"):
+        sys.modules.setdefault(m, MagicMock())
+    os.chdir(REF)
+    sys.path.insert(0, os.path.join(REF, "scripts"))
+    import hifigan                                   # noqa
+    from model.modules import LengthRegulator        # noqa
+    from utils.tools import get_mask_from_lengths, pad  # noqa
+    from utils.model import vocoder_infer            # noqa
+    return hifigan, LengthRegulator, get_mask_from_lengths, vocoder_infer
+
+
+def sd_sha256(sd):
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        h.update(k.encode())
+        h.update(sd[k].contiguous().numpy().tobytes())
+    return h.hexdigest()
+
+
+def main():
+    torch.set_num_threads(8)
+    hifigan, LengthRegulator, get_mask_from_lengths, vocoder_infer = import_reference()
+    h = hifigan.AttrDict(json.load(open(os.path.join(REF, "scripts/hifigan/config.json"))))
+
+    # ---- Generator, folded 156-key checkpoint -------------------------------------------
+    seed = 1234
+    sd = seeded_state_dict(seed)
+    gen = hifigan.Generator(h)
+    gen.eval()
+    gen.remove_weight_norm()
+    gen.load_state_dict(sd)
+    for name, (B, T, kind) in {"a": (2, 12, "logmel"), "b": (1, 33, "randn"),
+                               "c": (3, 1, "logmel")}.items():
+        mel = synthetic_mel(B, T, seed=7 + B, kind=kind)
+        with torch.no_grad():
+            wav = gen(mel)
+        np.savez_compressed(os.path.join(HERE, f"generator_{name}.npz"), seed=seed,
+                            weights_sha256=sd_sha256(sd), mel=mel.numpy(), wav=wav.numpy())
+        print("generator", name, tuple(wav.shape), float(wav.mean()), float(wav.std()))
+
+    # ---- Generator, 234-key weight_norm checkpoint through get_vocoder's sequence ---------
+    sd_wn = seeded_state_dict(4321, weight_norm=True)
+    # make g differ from ||v|| so the fold is actually exercised
+    for k in sd_wn:
+        if k.endswith("weight_g"):
+            sd_wn[k] = sd_wn[k] * (1.0 + 0.25 * torch.sin(torch.arange(sd_wn[k].numel()).float()
+                                                            ).reshape(sd_wn[k].shape))
+    gen2 = hifigan.Generator(h)
+    gen2.load_state_dict(sd_wn)      # utils/model.py:65
+    gen2.eval()
+    gen2.remove_weight_norm()        # utils/model.py:67
+    mel = synthetic_mel(2, 9, seed=11)
+    lengths = [9 * 256, 5 * 256 + 17]
+    wavs = vocoder_infer(mel, gen2, {"vocoder": {"model": "HiFi-GAN"}}, {}, lengths=lengths,
+                         Normalize=False)      # utils/model.py:73-98
+    folded = {k: v.detach().clone() for k, v in gen2.state_dict().items()}
+    np.savez_compressed(os.path.join(HERE, "vocoder_infer_wn.npz"), seed=4321,
+                        weights_sha256=sd_sha256(sd_wn), folded_sha256=sd_sha256(folded),
+                        conv_pre_w=folded["conv_pre.weight"].numpy()[:4],
+                        ups0_w=folded["ups.0.weight"].numpy()[:2],
+                        mel=mel.numpy(), lengths=np.array(lengths),
+                        wav0=wavs[0], wav1=wavs[1])
+    print("vocoder_infer", [w.shape for w in wavs])
+
+    # ---- LengthRegulator edge cases (modules.py:132-159) -------------------------------
+    lr = LengthRegulator()
+    g = torch.Generator().manual_seed(0)
+    cases = {}
+    x = torch.randn(4, 6, 8, generator=g)
+    cases["int_basic"] = (x, torch.randint(0, 5, (4, 6), generator=g), None)
+    cases["int_maxlen_pad"] = (x, torch.randint(0, 5, (4, 6), generator=g), 40)
+    cases["int_maxlen_crop"] = (x, torch.randint(1, 6, (4, 6), generator=g), 7)
+    cases["maxlen_zero_falsy"] = (x, torch.randint(0, 5, (4, 6), generator=g), 0)
+    cases["float_trunc"] = (x, torch.tensor([[0.0, 0.9, 1.0, 1.99, 2.5, 3.0001],
+                                             [-0.0, -0.5, -1.5, -3.0, 4.7, 1e-3],
+                                             [2.0, 2.0, 2.0, 2.0, 2.0, 2.0],
+                                             [0.5, 0.5, 0.5, 0.5, 0.5, 7.999]]), None)
+    cases["all_zero"] = (x, torch.zeros(4, 6), None)
+    cases["one_row_empty"] = (x, torch.tensor([[1, 2, 0, 0, 3, 1], [0, 0, 0, 0, 0, 0],
+                                               [5, 0, 0, 0, 0, 0], [0, 0, 0, 0, 0, 9]]), None)
+    cases["negative_int"] = (x, torch.tensor([[-1, 2, -3, 0, 3, 1]] * 4), None)
+    xb = torch.randn(64, 32, 256, generator=torch.Generator().manual_seed(3))   # regenerated in tests
+    cases["cfg3_int"] = (xb, torch.randint(0, 25, (64, 32), generator=g), None)
+    logd = torch.randn(64, 32, generator=g)
+    dur_f = torch.clamp(torch.round(torch.exp(logd) - 1) * 1.5, min=0)   # modules.py:110-113
+    cases["cfg3_float_maxlen1000"] = (xb, dur_f, 1000)
+    cases["bf16_passthrough"] = (x.to(torch.bfloat16), torch.randint(0, 5, (4, 6), generator=g), None)
+    out = {}
+    for name, (xx, dd, ml) in cases.items():
+        y, mel_len = lr(xx, dd, ml)
+        assert mel_len.dtype == torch.int64
+        big = xx.numel() > 100000      # config-3 sized cases: store digests, not 60 MB of frames
+        if not big:
+            out[f"{name}.x"] = xx.float().numpy()
+        out[f"{name}.x_is_bf16"] = np.array(xx.dtype == torch.bfloat16)
+        out[f"{name}.dur"] = dd.numpy()
+        out[f"{name}.max_len"] = np.array(-1 if ml is None else ml)
+        if big:
+            out[f"{name}.out_sha256"] = np.array(hashlib.sha256(y.contiguous().numpy().tobytes()).hexdigest())
+            out[f"{name}.out_shape"] = np.array(y.shape)
+        else:
+            out[f"{name}.out"] = y.float().numpy()
+        out[f"{name}.out_is_bf16"] = np.array(y.dtype == torch.bfloat16)
+        out[f"{name}.mel_len"] = mel_len.numpy()
+        if int(mel_len.max()) > 0:
+            out[f"{name}.mask"] = get_mask_from_lengths(mel_len).numpy()   # tools.py:164-171
+        print("LR", name, tuple(y.shape), mel_len.tolist()[:6])
+    out["round.logd"] = logd.numpy()
+    out["round.dur"] = dur_f.numpy()
+    np.savez_compressed(os.path.join(HERE, "length_regulator.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,103 @@
+"""The oracle against the fixtures produced by the reference itself (CPU, no GPU)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import hifigan_oracle as ho
+from oracle import length_regulator_oracle as lro
+from oracle.emulate import generator_forward_emulated, snr_db
+from visual_onoma_to_wave_b200.synthetic import seeded_state_dict, FLOP_PER_FRAME
+
+from helpers import sd_sha256, lr_cases, check_lr_output
+
+
+@pytest.fixture(scope="module")
+def sd1234():
+    return seeded_state_dict(1234)
+
+
+@pytest.mark.parametrize("case", ["a", "b", "c"])
+def test_generator_oracle_matches_reference_golden(golden_dir, sd1234, case):
+    g = np.load(os.path.join(golden_dir, f"generator_{case}.npz"))
+    assert sd_sha256(sd1234) == str(g["weights_sha256"])
+    wav = ho.generator_forward(sd1234, torch.from_numpy(g["mel"]))
+    assert wav.shape == g["wav"].shape
+    # same library calls in the same order; allow for thread-count dependent summation order
+    np.testing.assert_allclose(wav.numpy(), g["wav"], rtol=0, atol=2e-6)
+
+
+def test_generator_oracle_fp64_arbiter(golden_dir, sd1234):
+    g = np.load(os.path.join(golden_dir, "generator_a.npz"))
+    wav64 = ho.generator_forward(sd1234, torch.from_numpy(g["mel"]).double())
+    assert np.abs(wav64.numpy() - g["wav"]).max() < 1e-6
+
+
+def test_weight_norm_fold_and_vocoder_infer_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "vocoder_infer_wn.npz"))
+    sd = seeded_state_dict(4321, weight_norm=True)
+    for k in sd:
+        if k.endswith("weight_g"):
+            sd[k] = sd[k] * (1.0 + 0.25 * torch.sin(torch.arange(sd[k].numel()).float()).reshape(sd[k].shape))
+    assert sd_sha256(sd) == str(g["weights_sha256"])
+    folded = ho.fold_weight_norm(sd)
+    assert len(sd) == 234 and len(folded) == 156
+    assert sd_sha256(folded) == str(g["folded_sha256"])          # bit-equal fold
+    np.testing.assert_array_equal(folded["conv_pre.weight"].numpy()[:4], g["conv_pre_w"])
+    np.testing.assert_array_equal(folded["ups.0.weight"].numpy()[:2], g["ups0_w"])
+    wav = ho.generator_forward(sd, torch.from_numpy(g["mel"])).squeeze(1).numpy()
+    lengths = g["lengths"]
+    np.testing.assert_allclose(wav[0][: lengths[0]], g["wav0"], atol=2e-6, rtol=0)
+    np.testing.assert_allclose(wav[1][: lengths[1]], g["wav1"], atol=2e-6, rtol=0)
+
+
+def test_flop_count():
+    assert ho.count_flops(1) == FLOP_PER_FRAME == 614_105_088
+    assert ho.count_flops(172) == 105_626_075_136
+
+
+def test_numpy_conv_restatement_matches_torch():
+    """Pins what F.conv1d / F.conv_transpose1d mean, independently of torch (small case)."""
+    from oracle.np_conv import conv1d_np, conv_transpose1d_np, conv_transpose1d_polyphase_np
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((2, 6, 37))
+    w = rng.standard_normal((5, 6, 7))
+    b = rng.standard_normal(5)
+    for d in (1, 3, 5):
+        ref = torch.nn.functional.conv1d(torch.from_numpy(x), torch.from_numpy(w), torch.from_numpy(b),
+                                         padding=ho.get_padding(7, d), dilation=d).numpy()
+        np.testing.assert_allclose(conv1d_np(x, w, b, ho.get_padding(7, d), d), ref, atol=1e-12)
+    for (k, s) in ((16, 8), (4, 2)):
+        wt = rng.standard_normal((6, 5, k))
+        ref = torch.nn.functional.conv_transpose1d(torch.from_numpy(x), torch.from_numpy(wt), torch.from_numpy(b),
+                                                   stride=s, padding=(k - s) // 2).numpy()
+        np.testing.assert_allclose(conv_transpose1d_np(x, wt, b, s, (k - s) // 2), ref, atol=1e-12)
+        np.testing.assert_allclose(conv_transpose1d_polyphase_np(x, wt, b, s), ref, atol=1e-12)
+
+
+def test_length_regulator_oracle_matches_reference_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "length_regulator.npz"))
+    n = 0
+    for name, x, dur, ml in lr_cases(g):
+        if x.dtype == torch.bfloat16:
+            xn = x.view(torch.int16).numpy()          # bitwise copy semantics
+            out, mel_len = lro.length_regulate(xn, dur, ml)
+            out_t = torch.from_numpy(out).view(torch.bfloat16)
+        else:
+            out, mel_len = lro.length_regulate(x.numpy(), dur, ml)
+            out_t = torch.from_numpy(out)
+        check_lr_output(g, name, out_t, mel_len)
+        if f"{name}.mask" in g.files:
+            np.testing.assert_array_equal(lro.get_mask_from_lengths(mel_len), g[f"{name}.mask"])
+        n += 1
+    assert n == 11
+    np.testing.assert_array_equal(lro.round_durations(g["round.logd"], 1.5), g["round.dur"])
+
+
+def test_emulated_bf16_pipeline_is_inside_tolerance(golden_dir, sd1234):
+    """The numerics plan (bf16 operands, fp32 accumulate + fp32 residual) clears 40 dB."""
+    g = np.load(os.path.join(golden_dir, "generator_a.npz"))
+    mel = torch.from_numpy(g["mel"])
+    emu = generator_forward_emulated(sd1234, mel, mode="bf16", residual="fp32")
+    assert snr_db(torch.from_numpy(g["wav"]), emu) > 40.0

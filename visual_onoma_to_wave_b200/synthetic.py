@@ -1,0 +1,77 @@
+"""Deterministic synthetic weights / inputs for benchmarks, smoke and tests.
+
+No checkpoint ships with the reference (generator_universal.pth.tar is a missing blob,
+SURVEY.md facts table), so every number in this repo is on random-init weights.  The
+reference's random init is nn.Conv1d's default, U(-1/sqrt(fan_in), 1/sqrt(fan_in)):
+``init_weights`` (scripts/hifigan/models.py:10-13) writes into the recomputed ``.weight``
+of a weight_norm module and is lost.  This module reproduces those magnitudes without
+touching the reference, so the same weights exist on the GPU box.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict
+
+import torch
+
+V1_CONFIG = {  # scripts/hifigan/config.json:11-15,21,24
+    "upsample_rates": [8, 8, 2, 2],
+    "upsample_kernel_sizes": [16, 16, 4, 4],
+    "upsample_initial_channel": 512,
+    "resblock_kernel_sizes": [3, 7, 11],
+    "resblock_dilation_sizes": [[1, 3, 5], [1, 3, 5], [1, 3, 5]],
+    "sampling_rate": 22050,
+    "hop_size": 256,
+}
+
+FLOP_PER_FRAME = 614_105_088
+
+
+def layer_shapes(cfg=V1_CONFIG):
+    """name -> (weight shape, is ConvTranspose1d), in state-dict order (models.py:113-145)."""
+    c0 = cfg["upsample_initial_channel"]
+    shapes = {"conv_pre": ((c0, 80, 7), False)}
+    nk = len(cfg["resblock_kernel_sizes"])
+    ch = c0
+    for i, k in enumerate(cfg["upsample_kernel_sizes"]):
+        shapes[f"ups.{i}"] = ((c0 >> i, c0 >> (i + 1), k), True)
+    for i in range(len(cfg["upsample_rates"])):
+        ch = c0 >> (i + 1)
+        for j, rk in enumerate(cfg["resblock_kernel_sizes"]):
+            for grp in ("convs1", "convs2"):
+                for m in range(3):
+                    shapes[f"resblocks.{i * nk + j}.{grp}.{m}"] = ((ch, ch, rk), False)
+    shapes["conv_post"] = ((1, ch, 7), False)
+    return shapes
+
+
+def seeded_state_dict(seed: int, cfg=V1_CONFIG, weight_norm: bool = False) -> Dict[str, torch.Tensor]:
+    """234-key {bias, weight_g, weight_v} (weight_norm=True, g = ||v||) or 156-key folded."""
+    gen = torch.Generator().manual_seed(seed)
+    sd: Dict[str, torch.Tensor] = {}
+    for name, (shape, transposed) in layer_shapes(cfg).items():
+        bound = 1.0 / math.sqrt(shape[1] * shape[2])   # torch fan_in = size(1) * k
+        w = (torch.rand(shape, generator=gen) * 2 - 1) * bound
+        nb = shape[1] if transposed else shape[0]
+        b = (torch.rand(nb, generator=gen) * 2 - 1) * bound
+        sd[f"{name}.bias"] = b
+        if weight_norm:
+            sd[f"{name}.weight_g"] = w.reshape(shape[0], -1).norm(dim=1).reshape(shape[0], 1, 1)
+            sd[f"{name}.weight_v"] = w
+        else:
+            sd[f"{name}.weight"] = w
+    return sd
+
+
+def synthetic_mel(B: int, T: int, seed: int = 0, kind: str = "logmel") -> torch.Tensor:
+    """[B,80,T] fp32.  'logmel' = rand*13.5-11.5 (floor ln 1e-5)."""
+    gen = torch.Generator().manual_seed(seed)
+    if kind == "logmel":
+        return torch.rand(B, 80, T, generator=gen) * 13.5 - 11.5
+    return torch.randn(B, 80, T, generator=gen)
+
+
+def synthetic_durations(B: int, T_src: int, seed: int = 0, hi: int = 25) -> torch.Tensor:
+    """int64 [B,T_src] ~ U{0..hi-1} (config 3)."""
+    gen = torch.Generator().manual_seed(seed)
+    return torch.randint(0, hi, (B, T_src), generator=gen)
