@@ -1,0 +1,149 @@
+/*
+ * vo2w.h -- C ABI of libvo2w.so: the B200 (sm_100a) synthesis hot path of
+ * sarulab-speech/visual-onoma-to-wave (HiFi-GAN V1 Generator + LengthRegulator).
+ *
+ * The reference is pure Python/PyTorch and has no FFI of its own; each entry point
+ * below names the reference interface it replaces (file:line under /root/reference).
+ * INTEGRATION.md shows the ctypes binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  `stream` is a cudaStream_t passed
+ *     as void* (0 = legacy default stream).
+ *   - device pointers unless the name says host.  The caller owns every buffer; the
+ *     library owns only the packed weights inside a vo2w_generator handle.
+ *   - return 0 on success, a negative VO2W_E_* code otherwise (the Python mirror raises
+ *     RuntimeError, which is the reference's only error convention).  vo2w_last_error()
+ *     returns a thread-local message for the last failure.
+ *   - there is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef VO2W_H
+#define VO2W_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VO2W_OK            0
+#define VO2W_E_INVALID    -1   /* bad argument (shape, dtype, alignment, null pointer) */
+#define VO2W_E_CUDA       -2   /* a CUDA call or kernel launch failed                */
+#define VO2W_E_WORKSPACE  -3   /* workspace too small                                */
+#define VO2W_E_NODEVICE   -4   /* no sm_100 device                                   */
+
+/* duration dtypes accepted by the LengthRegulator (reference: float32 from the duration
+ * predictor, scripts/model/modules.py:110-113; float/int64 targets, utils/tools.py:48-49) */
+#define VO2W_DUR_I32 0
+#define VO2W_DUR_I64 1
+#define VO2W_DUR_F32 2
+#define VO2W_DUR_F64 3
+
+/* precision modes of the Generator */
+#define VO2W_PREC_FP32 0   /* CUDA-core fp32 kernels: max-abs-err <= 1e-4 gate            */
+#define VO2W_PREC_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate: SNR >= 40 dB */
+
+/* HiFi-GAN hyper-parameters read by Generator.__init__ (scripts/hifigan/models.py:116-143,
+ * values from scripts/hifigan/config.json:11-15). */
+typedef struct vo2w_gen_config {
+    int32_t num_upsamples;              /* <= 4 */
+    int32_t upsample_rates[4];
+    int32_t upsample_kernel_sizes[4];
+    int32_t upsample_initial_channel;
+    int32_t num_kernels;                /* <= 3 */
+    int32_t resblock_kernel_sizes[3];
+    int32_t resblock_dilation_sizes[3][3];
+    int32_t num_mels;                   /* conv_pre hard-codes 80 (models.py:119) */
+} vo2w_gen_config;
+
+typedef struct vo2w_generator vo2w_generator;
+
+const char* vo2w_last_error(void);
+int  vo2w_version(void);
+/* 0 when a compute-capability-10.x device is current, else VO2W_E_NODEVICE. */
+int  vo2w_device_check(void);
+
+/* ---- HiFi-GAN Generator ------------------------------------------------------------
+ * Replaces hifigan.Generator.__init__ + load_state_dict + remove_weight_norm + .to(device)
+ * (scripts/hifigan/models.py:112-147,167-174; scripts/utils/model.py:56-68).
+ * `weights_host` is the FOLDED state-dict (weight_norm already removed, 156 tensors)
+ * concatenated as fp32 in state-dict order: conv_pre.{weight,bias}, ups.i.{weight,bias},
+ * resblocks.n.convs1.m.{weight,bias} (m=0..2), resblocks.n.convs2.m.{weight,bias},
+ * conv_post.{weight,bias} -- i.e. for every layer weight first, then bias, layers in
+ * the order Generator registers them.  `n_floats` is checked against the config. */
+int vo2w_generator_create(const vo2w_gen_config* cfg, const float* weights_host, size_t n_floats,
+                          int precision, vo2w_generator** out);
+int vo2w_generator_destroy(vo2w_generator* g);
+
+/* Bytes of device scratch forward() needs for a [B,80,T] batch. */
+size_t vo2w_generator_workspace_bytes(const vo2w_generator* g, int B, int T);
+
+/* Replaces Generator.forward (scripts/hifigan/models.py:149-165):
+ * mel fp32 [B,80,T] contiguous  ->  wav fp32 [B,1,T*prod(upsample_rates)].
+ * `ws_fresh` != 0 tells the library the workspace has not been used with this (B,T)
+ * before (it then zeroes the halo rows it relies on). */
+int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B, int T, float* wav,
+                           void* workspace, size_t workspace_bytes, int ws_fresh, void* stream);
+
+/* Same call with HOST buffers (the vocoder_infer seam, scripts/utils/model.py:73-98:
+ * host mel in, `.cpu().numpy()` out).  Copies through the caller's pinned or pageable
+ * memory on `stream` and synchronises it before returning.  wav_i16 (optional) receives
+ * (wav * max_wav_value) truncated to int16 as utils/model.py:83-86 does. */
+int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_host, int B, int T,
+                                float* wav_host, int16_t* wav_i16_host, float max_wav_value,
+                                void* workspace, size_t workspace_bytes, int ws_fresh,
+                                void* mel_dev, void* wav_dev, void* stream);
+
+/* Per-layer probe used by the known-answer tests: copies the fp32 activation named
+ * `tap` ("conv_pre", "ups.0", "resblocks.3", "mrf.1", ...) of the LAST forward into
+ * out_host as NCL [B,C,L].  Returns the element count, or a negative error. */
+long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap, float* out_host,
+                                   size_t capacity);
+
+/* Known-answer probe: ONE reference layer through one kernel family, NCL fp32 in/out.
+ * transposed = 0: nn.Conv1d(Cin, Cout, k, dilation=d, padding=d*(k-1)/2) (models.py:26-92)
+ * transposed = 1: nn.ConvTranspose1d(Cin, Cout, k=2s, stride=s, padding=s/2) (models.py:123-135)
+ * out = layer(leaky_relu(x, in_slope)) [+ res];  use_umma selects tcgen05 (1) or fp32 CUDA cores (0).
+ * w_host/bias_host in the torch layout, x/res/out on the device.  Synchronises `stream`. */
+int vo2w_debug_layer(int transposed, int use_umma, const float* w_host, const float* bias_host, int Cin,
+                     int Cout, int k, int dil_or_stride, const float* x_dev, int B, int L, float in_slope,
+                     const float* res_dev, float* out_dev, void* stream);
+
+/* Host-only probe of the weight packing (no device needed): meta[0..11] = {Cin, Cout, n_cols,
+ * n_tiles, phases_per_tile, halo_l, halo_r, n_items, w_tile_stride, up_s, w_elems, bias_elems},
+ * then per item {row_shift, n_off, n_size, zero_init, w_off}; w_out receives the packed bf16 bits.
+ * Pass w_out = NULL to query sizes.  The CPU tests replay the kernel's indexing from these. */
+int vo2w_debug_pack(int transposed, const float* w, const float* bias, int Cin, int Cout, int k,
+                    int dil_or_stride, int32_t* meta, uint16_t* w_out, size_t w_capacity,
+                    float* bias_out, size_t bias_capacity);
+
+/* Kernel launches issued by the last forward (bench.py's gpu_launches). */
+int vo2w_generator_last_launches(const vo2w_generator* g);
+
+/* ---- LengthRegulator -----------------------------------------------------------------
+ * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad
+ * (scripts/utils/tools.py:669-687).
+ *
+ * vo2w_lr_lengths: mel_len[b] = sum_i max(trunc(duration[b,i]), 0)  (int64, uncropped)
+ * and *max_len_dev = max_b mel_len[b].  One launch; the caller reads max_len back only
+ * when the reference would (max_len is None). */
+int vo2w_lr_lengths(const void* duration, int dur_dtype, int B, int T_src,
+                    int64_t* mel_len_dev, int64_t* max_len_dev, void* stream);
+
+/* out[b,p,:] = x[b,i,:] for cum[i] <= p < cum[i+1], zeros for p >= mel_len[b], rows
+ * beyond Lmax cropped.  x is [B,T_src,row_bytes] (any element type, copied bitwise),
+ * out is [B,Lmax,row_bytes].  mask (optional, uint8 [B,Lmax]) = p >= mel_len[b]
+ * (get_mask_from_lengths, scripts/utils/tools.py:164-171).  mel_len (optional) is
+ * rewritten with the uncropped lengths. */
+int vo2w_length_regulate(const void* x, const void* duration, int dur_dtype, int B, int T_src,
+                         size_t row_bytes, void* out, long long Lmax, int64_t* mel_len_dev,
+                         uint8_t* mask, void* stream);
+
+/* mask[b,p] = p >= lengths[b], p < max_len (scripts/utils/tools.py:164-171). */
+int vo2w_mask_from_lengths(const int64_t* lengths_dev, int B, long long max_len, uint8_t* mask,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VO2W_H */

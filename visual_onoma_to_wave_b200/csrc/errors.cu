@@ -1,0 +1,28 @@
+// error message storage + trivial entry points
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void vo2w_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* vo2w_last_error(void) { return g_err; }
+extern "C" int vo2w_version(void) { return 100; }
+
+extern "C" int vo2w_device_check(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        vo2w_set_error("no CUDA device");
+        return VO2W_E_NODEVICE;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10) {
+        vo2w_set_error("device is not sm_100 (compute capability 10.x)");
+        return VO2W_E_NODEVICE;
+    }
+    return VO2W_OK;
+}

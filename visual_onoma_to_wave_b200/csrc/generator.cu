@@ -1,0 +1,576 @@
+// HiFi-GAN V1 Generator on sm_100a: handle, workspace plan and the forward schedule.
+//
+// Replaces hifigan.Generator (scripts/hifigan/models.py:112-174) behind the C ABI of
+// include/vo2w.h.  Two precision modes share this schedule:
+//   VO2W_PREC_BF16  tcgen05 implicit-GEMM kernels (conv_umma.cu) on chunked bf16 operand
+//                   buffers with an fp32 residual stream;
+//   VO2W_PREC_FP32  CUDA-core fp32 kernels (conv_simt.cu) on plain NCL tensors.
+#include <map>
+#include <string>
+#include <vector>
+
+#include "conv_simt.cuh"
+#include "pack.cuh"
+
+namespace {
+
+struct LayerW {            // one reference layer inside the fp32 blob
+    size_t w_off, b_off;   // float offsets
+    int d0, d1, k;         // weight shape
+};
+
+struct StageBufs {         // per upsampling stage, offsets in bytes into the workspace
+    int C = 0;
+    long long L = 0, Lp = 0;
+    size_t x_f32 = 0;              // ups output, fp32 (residual for the first conv pair)
+    size_t xa = 0;                 // bf16 leaky-relu(x)
+    size_t xr[3] = {0, 0, 0};      // fp32 residual stream of ResBlock j
+    size_t ya[3] = {0, 0, 0};      // bf16 leaky-relu(residual stream)
+    size_t t[3] = {0, 0, 0};       // bf16 leaky-relu(conv1 output)
+    size_t mrf = 0;                // bf16 leaky-relu(MRF average) = operand of the next layer
+    size_t mrf_f32 = 0;            // debug tap only
+    // fp32 mode (NCL)
+    size_t r = 0, tt = 0, xs = 0;
+};
+
+struct Plan {
+    int B = 0, T = 0;
+    size_t melb = 0, a0 = 0, c0_f32 = 0;
+    StageBufs st[4];
+    size_t total = 0;
+};
+
+}  // namespace
+
+struct vo2w_generator {
+    vo2w_gen_config cfg;
+    int precision = 0;
+    bool debug_taps = false;
+    int n_stage = 0, nk = 0;
+    std::vector<LayerW> lw;        // conv_pre, ups[i], resblocks[n].convs1[m], .convs2[m], conv_post (state-dict order)
+    size_t n_floats = 0;
+    float* w_dev = nullptr;        // fp32 blob on the device (fp32 mode + biases)
+    // bf16 mode
+    PackedLayer conv_pre, conv_post, ups[4];
+    PackedLayer c1[12][3], c2[12][3];
+    float* mrf_bias[4] = {nullptr, nullptr, nullptr, nullptr};   // sum of the three convs2[2] biases
+    // last forward (debug taps, launch count)
+    Plan last;
+    void* last_ws = nullptr;
+    int last_launches = 0;
+};
+
+namespace {
+
+int idx_conv_pre() { return 0; }
+int idx_ups(int i) { return 1 + i; }
+int idx_rb(const vo2w_generator* g, int n, int grp, int m) { return 1 + g->n_stage + n * 6 + grp * 3 + m; }
+int idx_conv_post(const vo2w_generator* g) { return 1 + g->n_stage + g->n_stage * g->nk * 6; }
+
+int stage_channels(const vo2w_generator* g, int i) { return g->cfg.upsample_initial_channel >> (i + 1); }
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+Plan make_plan(const vo2w_generator* g, int B, int T) {
+    Plan p;
+    p.B = B;
+    p.T = T;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        size_t o = off;
+        off = align_up(off + bytes, 256);
+        return o;
+    };
+    const int C0 = g->cfg.upsample_initial_channel;
+    long long L = T;
+    if (g->precision == VO2W_PREC_BF16) {
+        const long long Lp0 = vo2w_padded_len(T);
+        p.melb = take((size_t)B * 80 * Lp0 * 2);
+        p.a0 = take((size_t)B * C0 * Lp0 * 2);
+        if (g->debug_taps) p.c0_f32 = take((size_t)B * C0 * T * 4);
+        for (int i = 0; i < g->n_stage; ++i) {
+            StageBufs& s = p.st[i];
+            L *= g->cfg.upsample_rates[i];
+            s.C = stage_channels(g, i);
+            s.L = L;
+            s.Lp = vo2w_padded_len(L);
+            const size_t f32b = (size_t)B * s.C * L * 4, bfb = (size_t)B * s.C * s.Lp * 2;
+            s.x_f32 = take(f32b);
+            s.xa = take(bfb);
+            for (int j = 0; j < g->nk; ++j) {
+                s.xr[j] = take(f32b);
+                s.ya[j] = take(bfb);
+                s.t[j] = take(bfb);
+            }
+            s.mrf = take(bfb);
+            if (g->debug_taps) s.mrf_f32 = take(f32b);
+        }
+    } else {
+        p.c0_f32 = take((size_t)B * C0 * T * 4);
+        for (int i = 0; i < g->n_stage; ++i) {
+            StageBufs& s = p.st[i];
+            L *= g->cfg.upsample_rates[i];
+            s.C = stage_channels(g, i);
+            s.L = L;
+            const size_t f32b = (size_t)B * s.C * L * 4;
+            s.x_f32 = take(f32b);
+            s.r = take(f32b);
+            s.tt = take(f32b);
+            s.xs = take(f32b);
+        }
+    }
+    p.total = off;
+    return p;
+}
+
+int build_layer_table(vo2w_generator* g, size_t n_floats) {
+    const vo2w_gen_config& c = g->cfg;
+    size_t off = 0;
+    auto add = [&](int d0, int d1, int k, int nbias) {
+        LayerW l;
+        l.w_off = off;
+        l.d0 = d0;
+        l.d1 = d1;
+        l.k = k;
+        off += (size_t)d0 * d1 * k;
+        l.b_off = off;
+        off += nbias;
+        g->lw.push_back(l);
+    };
+    const int C0 = c.upsample_initial_channel;
+    add(C0, 80, 7, C0);                                                     // conv_pre (models.py:118-120)
+    for (int i = 0; i < g->n_stage; ++i)                                    // ups (models.py:123-135)
+        add(C0 >> i, C0 >> (i + 1), c.upsample_kernel_sizes[i], C0 >> (i + 1));
+    for (int i = 0; i < g->n_stage; ++i)                                    // resblocks (models.py:137-143)
+        for (int j = 0; j < g->nk; ++j)
+            for (int grp = 0; grp < 2; ++grp)
+                for (int m = 0; m < 3; ++m) {
+                    const int ch = stage_channels(g, i);
+                    add(ch, ch, c.resblock_kernel_sizes[j], ch);
+                }
+    add(1, stage_channels(g, g->n_stage - 1), 7, 1);                        // conv_post (models.py:145)
+    VO2W_REQUIRE(off == n_floats, "generator_create: weight blob has %zu floats, config needs %zu", n_floats, off);
+    return VO2W_OK;
+}
+
+}  // namespace
+
+extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* weights_host, size_t n_floats,
+                                     int precision, vo2w_generator** out) {
+    VO2W_REQUIRE(cfg && weights_host && out, "generator_create: null argument");
+    VO2W_REQUIRE(precision == VO2W_PREC_FP32 || precision == VO2W_PREC_BF16, "generator_create: bad precision %d", precision);
+    VO2W_REQUIRE(cfg->num_upsamples >= 1 && cfg->num_upsamples <= 4, "generator_create: num_upsamples %d", cfg->num_upsamples);
+    VO2W_REQUIRE(cfg->num_kernels >= 1 && cfg->num_kernels <= 3, "generator_create: num_kernels %d", cfg->num_kernels);
+    VO2W_REQUIRE(cfg->num_mels == 80, "generator_create: conv_pre takes 80 mel bins (models.py:119)");
+    int rc = vo2w_device_check();
+    if (rc != VO2W_OK) return rc;
+    vo2w_generator* g = new vo2w_generator();
+    g->cfg = *cfg;
+    g->precision = precision;
+    g->n_stage = cfg->num_upsamples;
+    g->nk = cfg->num_kernels;
+    const char* dbg = getenv("VO2W_DEBUG_TAPS");
+    g->debug_taps = dbg && dbg[0] == '1';
+    g->n_floats = n_floats;
+    rc = build_layer_table(g, n_floats);
+    if (rc != VO2W_OK) { delete g; return rc; }
+#define VO2W_TRY(expr) do { int _rc = (expr); if (_rc != VO2W_OK) { vo2w_generator_destroy(g); return _rc; } } while (0)
+    if (cudaMalloc(&g->w_dev, n_floats * 4) != cudaSuccess ||
+        cudaMemcpy(g->w_dev, weights_host, n_floats * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+        vo2w_set_error("generator_create: uploading weights failed");
+        vo2w_generator_destroy(g);
+        return VO2W_E_CUDA;
+    }
+    if (precision == VO2W_PREC_BF16) {
+        const float* W = weights_host;
+        auto pc = [&](PackedLayer& L, int idx, int dil) {
+            const LayerW& l = g->lw[idx];
+            int r = pack_conv(L, W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, dil);
+            return r != VO2W_OK ? r : upload_layer(L);
+        };
+        VO2W_TRY(pc(g->conv_pre, idx_conv_pre(), 1));
+        VO2W_TRY(pc(g->conv_post, idx_conv_post(g), 1));
+        for (int i = 0; i < g->n_stage; ++i) {
+            const LayerW& l = g->lw[idx_ups(i)];
+            VO2W_TRY(pack_convT(g->ups[i], W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, cfg->upsample_rates[i]));
+            VO2W_TRY(upload_layer(g->ups[i]));
+            const int ch = stage_channels(g, i);
+            std::vector<float> bsum(ch, 0.f);
+            for (int j = 0; j < g->nk; ++j) {
+                const int n = i * g->nk + j;
+                for (int m = 0; m < 3; ++m) {
+                    VO2W_TRY(pc(g->c1[n][m], idx_rb(g, n, 0, m), cfg->resblock_dilation_sizes[j][m]));
+                    VO2W_TRY(pc(g->c2[n][m], idx_rb(g, n, 1, m), 1));
+                }
+                const float* b = W + g->lw[idx_rb(g, n, 1, 2)].b_off;
+                for (int c = 0; c < ch; ++c) bsum[c] += b[c];
+            }
+            if (cudaMalloc(&g->mrf_bias[i], ch * 4) != cudaSuccess ||
+                cudaMemcpy(g->mrf_bias[i], bsum.data(), ch * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+                vo2w_set_error("generator_create: uploading bias failed");
+                vo2w_generator_destroy(g);
+                return VO2W_E_CUDA;
+            }
+        }
+    }
+#undef VO2W_TRY
+    *out = g;
+    return VO2W_OK;
+}
+
+extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
+    if (!g) return VO2W_OK;
+    if (g->w_dev) cudaFree(g->w_dev);
+    free_layer(g->conv_pre);
+    free_layer(g->conv_post);
+    for (int i = 0; i < 4; ++i) {
+        free_layer(g->ups[i]);
+        if (g->mrf_bias[i]) cudaFree(g->mrf_bias[i]);
+    }
+    for (int n = 0; n < 12; ++n)
+        for (int m = 0; m < 3; ++m) {
+            free_layer(g->c1[n][m]);
+            free_layer(g->c2[n][m]);
+        }
+    delete g;
+    return VO2W_OK;
+}
+
+extern "C" size_t vo2w_generator_workspace_bytes(const vo2w_generator* g, int B, int T) {
+    if (!g || B <= 0 || T <= 0) return 0;
+    return make_plan(g, B, T).total;
+}
+
+extern "C" int vo2w_generator_last_launches(const vo2w_generator* g) { return g ? g->last_launches : 0; }
+
+// ---------------------------------------------------------------------------------------
+// forward schedules
+// ---------------------------------------------------------------------------------------
+namespace {
+
+#define VO2W_RUN(expr) do { int _rc = (expr); if (_rc != VO2W_OK) return _rc; ++g->last_launches; } while (0)
+
+// Generator.forward (models.py:149-165) on the tcgen05 path.
+int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
+    const int B = p.B, T = p.T;
+    auto bf = [&](size_t off) { return (__nv_bfloat16*)(ws + off); };
+    auto f32 = [&](size_t off) { return (float*)(ws + off); };
+
+    // mel [B,80,T] fp32 -> operand buffer
+    VO2W_RUN(pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
+    {   // x = conv_pre(mel); next consumer is leaky_relu(0.1) -> ups[0]
+        const PackedLayer* L[1] = {&g->conv_pre};
+        const __nv_bfloat16* in[1] = {bf(p.melb)};
+        EpilogueSpec ep;
+        ep.out_bf16 = bf(p.a0);
+        ep.out_slope = 0.1f;
+        if (g->debug_taps) ep.out_f32 = f32(p.c0_f32);
+        VO2W_RUN(launch_layers(L, in, 1, B, T, ep, st));
+    }
+    const __nv_bfloat16* stage_in = bf(p.a0);
+    long long L_in = T;
+    for (int i = 0; i < g->n_stage; ++i) {
+        const StageBufs& s = p.st[i];
+        {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM, writes fp32 x and bf16 leaky_relu(x)
+            const PackedLayer* L[1] = {&g->ups[i]};
+            const __nv_bfloat16* in[1] = {stage_in};
+            EpilogueSpec ep;
+            ep.out_f32 = f32(s.x_f32);
+            ep.out_bf16 = bf(s.xa);
+            ep.out_slope = 0.1f;
+            VO2W_RUN(launch_layers(L, in, 1, B, (int)L_in, ep, st));
+        }
+        for (int m = 0; m < 3; ++m) {
+            for (int j = 0; j < g->nk; ++j) {   // xt = c1(leaky_relu(x)); operand of c2 is leaky_relu(xt)
+                const int n = i * g->nk + j;
+                const PackedLayer* L[1] = {&g->c1[n][m]};
+                const __nv_bfloat16* in[1] = {m == 0 ? bf(s.xa) : bf(s.ya[j])};
+                EpilogueSpec ep;
+                ep.out_bf16 = bf(s.t[j]);
+                ep.out_slope = 0.1f;
+                VO2W_RUN(launch_layers(L, in, 1, B, (int)s.L, ep, st));
+            }
+            if (m < 2) {
+                for (int j = 0; j < g->nk; ++j) {   // x = c2(leaky_relu(xt)) + x
+                    const int n = i * g->nk + j;
+                    const PackedLayer* L[1] = {&g->c2[n][m]};
+                    const __nv_bfloat16* in[1] = {bf(s.t[j])};
+                    EpilogueSpec ep;
+                    ep.res[0] = m == 0 ? f32(s.x_f32) : f32(s.xr[j]);
+                    ep.n_res = 1;
+                    ep.out_f32 = f32(s.xr[j]);
+                    ep.out_bf16 = bf(s.ya[j]);
+                    ep.out_slope = 0.1f;
+                    VO2W_RUN(launch_layers(L, in, 1, B, (int)s.L, ep, st));
+                }
+            } else {
+                // last conv of all ResBlocks of the stage in ONE launch: the three c2 accumulate into
+                // the same TMEM tile; epilogue adds the three residual streams and divides by
+                // num_kernels (xs = sum_j resblock_j(x); x = xs / num_kernels, models.py:154-160).
+                const PackedLayer* L[3];
+                const __nv_bfloat16* in[3];
+                EpilogueSpec ep;
+                for (int j = 0; j < g->nk; ++j) {
+                    L[j] = &g->c2[i * g->nk + j][2];
+                    in[j] = bf(s.t[j]);
+                    ep.res[j] = f32(s.xr[j]);
+                }
+                ep.n_res = g->nk;
+                ep.bias = g->mrf_bias[i];
+                ep.div = (float)g->nk;
+                ep.out_bf16 = bf(s.mrf);
+                ep.out_slope = i + 1 < g->n_stage ? 0.1f : 0.01f;   // F.leaky_relu(x) default slope before conv_post
+                if (g->debug_taps) ep.out_f32 = f32(s.mrf_f32);
+                VO2W_RUN(launch_layers(L, in, g->nk, B, (int)s.L, ep, st));
+            }
+        }
+        stage_in = bf(s.mrf);
+        L_in = s.L;
+    }
+    {   // wav = tanh(conv_post(leaky_relu(x)))
+        const PackedLayer* L[1] = {&g->conv_post};
+        const __nv_bfloat16* in[1] = {stage_in};
+        EpilogueSpec ep;
+        ep.out_wave = wav;
+        VO2W_RUN(launch_layers(L, in, 1, B, (int)L_in, ep, st));
+    }
+    return VO2W_OK;
+}
+
+// Same schedule on the fp32 CUDA-core kernels (NCL tensors).
+int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
+    const int B = p.B, T = p.T;
+    auto f32 = [&](size_t off) { return (float*)(ws + off); };
+    auto W = [&](int idx) { return g->w_dev + g->lw[idx].w_off; };
+    auto Bi = [&](int idx) { return g->w_dev + g->lw[idx].b_off; };
+    SimtConv c;
+    memset(&c, 0, sizeof(c));
+    c.B = B;
+    c.stride = 1;
+    c.div = 1.f;
+    {
+        const LayerW& l = g->lw[idx_conv_pre()];
+        SimtConv q = c;
+        q.x = mel; q.w = W(0); q.bias = Bi(0); q.out = f32(p.c0_f32);
+        q.Cin = l.d1; q.Cout = l.d0; q.L = T; q.k = l.k; q.dil = 1; q.pad = 3; q.in_slope = 1.f;
+        VO2W_RUN(simt_conv1d(q, st));
+    }
+    const float* x_in = f32(p.c0_f32);
+    long long L_in = T;
+    for (int i = 0; i < g->n_stage; ++i) {
+        const StageBufs& s = p.st[i];
+        {
+            const int idx = idx_ups(i);
+            const LayerW& l = g->lw[idx];
+            SimtConv q = c;
+            q.x = x_in; q.w = W(idx); q.bias = Bi(idx); q.out = f32(s.x_f32);
+            q.Cin = l.d0; q.Cout = l.d1; q.L = (int)L_in; q.k = l.k; q.stride = g->cfg.upsample_rates[i];
+            q.pad = (l.k - q.stride) / 2; q.in_slope = 0.1f;
+            VO2W_RUN(simt_convt1d(q, st));
+        }
+        for (int j = 0; j < g->nk; ++j) {
+            const int n = i * g->nk + j;
+            const int k = g->cfg.resblock_kernel_sizes[j];
+            for (int m = 0; m < 3; ++m) {
+                const int d = g->cfg.resblock_dilation_sizes[j][m];
+                const float* xin = m == 0 ? f32(s.x_f32) : f32(s.r);
+                SimtConv q = c;
+                int idx = idx_rb(g, n, 0, m);
+                q.x = xin; q.w = W(idx); q.bias = Bi(idx); q.out = f32(s.tt);
+                q.Cin = q.Cout = s.C; q.L = (int)s.L; q.k = k; q.dil = d; q.pad = d * (k - 1) / 2; q.in_slope = 0.1f;
+                VO2W_RUN(simt_conv1d(q, st));
+                idx = idx_rb(g, n, 1, m);
+                q.x = f32(s.tt); q.w = W(idx); q.bias = Bi(idx); q.dil = 1; q.pad = (k - 1) / 2;
+                q.res = xin;
+                if (m < 2) {
+                    q.out = f32(s.r);
+                } else {            // xs (+)= resblock_j(x); after the last one x = xs / num_kernels
+                    q.out = f32(s.xs);
+                    q.accum = j == 0 ? 0 : 1;
+                    if (j == g->nk - 1 && g->nk > 1) { q.accum = 2; q.div = (float)g->nk; }
+                }
+                VO2W_RUN(simt_conv1d(q, st));
+            }
+        }
+        x_in = f32(s.xs);
+        L_in = s.L;
+    }
+    {
+        const int idx = idx_conv_post(g);
+        const LayerW& l = g->lw[idx];
+        SimtConv q = c;
+        q.x = x_in; q.w = W(idx); q.bias = Bi(idx); q.out = wav;
+        q.Cin = l.d1; q.Cout = 1; q.L = (int)L_in; q.k = l.k; q.dil = 1; q.pad = 3; q.in_slope = 0.01f; q.tanh_out = 1;
+        VO2W_RUN(simt_conv1d(q, st));
+    }
+    return VO2W_OK;
+}
+
+}  // namespace
+
+extern "C" int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B, int T, float* wav, void* workspace,
+                                      size_t workspace_bytes, int ws_fresh, void* stream) {
+    VO2W_REQUIRE(g && mel && wav, "generator_forward: null argument");
+    VO2W_REQUIRE(B > 0 && T > 0, "generator_forward: empty batch (B=%d T=%d)", B, T);
+    VO2W_REQUIRE(B <= 65535, "generator_forward: batch %d exceeds grid.z", B);
+    const Plan p = make_plan(g, B, T);
+    if (workspace_bytes < p.total || !workspace) {
+        vo2w_set_error("generator_forward: workspace %zu bytes, need %zu", workspace_bytes, p.total);
+        return VO2W_E_WORKSPACE;
+    }
+    VO2W_REQUIRE(((uintptr_t)workspace & 255) == 0, "generator_forward: workspace must be 256-byte aligned");
+    VO2W_REQUIRE(((uintptr_t)mel & 15) == 0 && ((uintptr_t)wav & 15) == 0, "generator_forward: mel/wav must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    g->last = p;
+    g->last_ws = workspace;
+    g->last_launches = 0;
+    if (ws_fresh && g->precision == VO2W_PREC_BF16)   // halo / tail rows of the operand buffers must read as zero
+        VO2W_CUDA_OK(cudaMemsetAsync(workspace, 0, p.total, st));
+    if (g->precision == VO2W_PREC_BF16) return forward_bf16(g, p, mel, wav, (uint8_t*)workspace, st);
+    return forward_fp32(g, p, mel, wav, (uint8_t*)workspace, st);
+}
+
+namespace {
+__global__ void wav_to_i16_kernel(const float* __restrict__ w, short* __restrict__ o, float scale, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = (short)(int)(w[i] * scale);   // numpy astype("int16") of in-range floats truncates toward zero
+}
+}  // namespace
+
+extern "C" int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
+                                           int16_t* wav_i16_host, float max_wav_value, void* workspace,
+                                           size_t workspace_bytes, int ws_fresh, void* mel_dev, void* wav_dev,
+                                           void* stream) {
+    VO2W_REQUIRE(g && mel_host && mel_dev && wav_dev, "generator_forward_host: null argument");
+    VO2W_REQUIRE(wav_host || wav_i16_host, "generator_forward_host: no output buffer");
+    VO2W_REQUIRE(B > 0 && T > 0, "generator_forward_host: empty batch");
+    cudaStream_t st = (cudaStream_t)stream;
+    long long up = 1;
+    for (int i = 0; i < g->n_stage; ++i) up *= g->cfg.upsample_rates[i];
+    const long long n_out = (long long)B * T * up;
+    VO2W_CUDA_OK(cudaMemcpyAsync(mel_dev, mel_host, (size_t)B * 80 * T * 4, cudaMemcpyHostToDevice, st));
+    int rc = vo2w_generator_forward(g, (const float*)mel_dev, B, T, (float*)wav_dev, workspace, workspace_bytes, ws_fresh,
+                                    stream);
+    if (rc != VO2W_OK) return rc;
+    if (wav_i16_host) {
+        // int16 samples reuse the head of the workspace (the mel operand buffer is dead by now)
+        VO2W_REQUIRE((size_t)n_out * 2 <= workspace_bytes, "generator_forward_host: workspace too small for int16");
+        wav_to_i16_kernel<<<(unsigned)vo2w_ceil_div(n_out, 256), 256, 0, st>>>((const float*)wav_dev, (short*)workspace,
+                                                                              max_wav_value, n_out);
+        VO2W_CUDA_OK(cudaGetLastError());
+        ++g->last_launches;
+        VO2W_CUDA_OK(cudaMemcpyAsync(wav_i16_host, workspace, (size_t)n_out * 2, cudaMemcpyDeviceToHost, st));
+    }
+    if (wav_host) VO2W_CUDA_OK(cudaMemcpyAsync(wav_host, wav_dev, (size_t)n_out * 4, cudaMemcpyDeviceToHost, st));
+    VO2W_CUDA_OK(cudaStreamSynchronize(st));
+    return VO2W_OK;
+}
+
+extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap, float* out_host, size_t capacity) {
+    VO2W_REQUIRE(g && tap && out_host, "debug_tap: null argument");
+    VO2W_REQUIRE(g->last_ws, "debug_tap: no forward has run");
+    const Plan& p = g->last;
+    uint8_t* ws = (uint8_t*)g->last_ws;
+    const std::string name(tap);
+    size_t off = 0;
+    int C = 0;
+    long long L = 0;
+    bool found = false;
+    const bool bf = g->precision == VO2W_PREC_BF16;
+    if (name == "conv_pre" && (!bf || g->debug_taps)) {
+        off = p.c0_f32; C = g->cfg.upsample_initial_channel; L = p.T; found = true;
+    }
+    for (int i = 0; i < g->n_stage && !found; ++i) {
+        if (name == "ups." + std::to_string(i)) { off = p.st[i].x_f32; found = true; }
+        else if (name == "mrf." + std::to_string(i) && (!bf || g->debug_taps)) { off = bf ? p.st[i].mrf_f32 : p.st[i].xs; found = true; }
+        if (found) { C = p.st[i].C; L = p.st[i].L; }
+    }
+    VO2W_REQUIRE(found, "debug_tap: unknown or disabled tap '%s' (set VO2W_DEBUG_TAPS=1 before create)", tap);
+    const size_t n = (size_t)p.B * C * L;
+    VO2W_REQUIRE(n <= capacity, "debug_tap: need %zu floats, capacity %zu", n, capacity);
+    VO2W_CUDA_OK(cudaDeviceSynchronize());
+    if (bf) {
+        float* tmp = nullptr;
+        VO2W_CUDA_OK(cudaMalloc(&tmp, n * 4));
+        int rc = unchunk_f32((const float*)(ws + off), tmp, p.B, C, C, (int)L, 0);
+        if (rc == VO2W_OK && cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = VO2W_E_CUDA;
+        cudaFree(tmp);
+        if (rc != VO2W_OK) return rc;
+    } else {
+        VO2W_CUDA_OK(cudaMemcpy(out_host, ws + off, n * 4, cudaMemcpyDeviceToHost));
+    }
+    return (long long)n;
+}
+
+// ---------------------------------------------------------------------------------------
+// Known-answer probe: ONE reference layer through either kernel family, NCL fp32 in/out.
+// transposed = 0: nn.Conv1d(Cin,Cout,k,dilation=d,padding=d(k-1)/2); 1: nn.ConvTranspose1d(Cin,Cout,k=2s,stride=s,padding=s/2)
+// y = layer(leaky_relu(x, in_slope)) [+ res]
+// ---------------------------------------------------------------------------------------
+extern "C" int vo2w_debug_layer(int transposed, int use_umma, const float* w_host, const float* bias_host, int Cin,
+                                int Cout, int k, int dil_or_stride, const float* x_dev, int B, int L, float in_slope,
+                                const float* res_dev, float* out_dev, void* stream) {
+    VO2W_REQUIRE(w_host && bias_host && x_dev && out_dev, "debug_layer: null argument");
+    int rc = vo2w_device_check();
+    if (rc != VO2W_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int s = transposed ? dil_or_stride : 1;
+    const long long Lo = (long long)L * s;
+    const size_t wn = (size_t)Cin * Cout * k;
+    if (!use_umma) {
+        float *w = nullptr, *b = nullptr;
+        VO2W_CUDA_OK(cudaMalloc(&w, wn * 4));
+        VO2W_CUDA_OK(cudaMalloc(&b, (size_t)Cout * 4));
+        VO2W_CUDA_OK(cudaMemcpyAsync(w, w_host, wn * 4, cudaMemcpyHostToDevice, st));
+        VO2W_CUDA_OK(cudaMemcpyAsync(b, bias_host, (size_t)Cout * 4, cudaMemcpyHostToDevice, st));
+        SimtConv q;
+        memset(&q, 0, sizeof(q));
+        q.x = x_dev; q.w = w; q.bias = b; q.res = res_dev; q.out = out_dev;
+        q.B = B; q.Cin = Cin; q.Cout = Cout; q.L = L; q.k = k; q.in_slope = in_slope; q.div = 1.f;
+        if (transposed) { q.stride = s; q.dil = 1; q.pad = (k - s) / 2; rc = simt_convt1d(q, st); }
+        else { q.stride = 1; q.dil = dil_or_stride; q.pad = q.dil * (k - 1) / 2; rc = simt_conv1d(q, st); }
+        cudaStreamSynchronize(st);
+        cudaFree(w);
+        cudaFree(b);
+        return rc;
+    }
+    VO2W_REQUIRE(res_dev == nullptr || !transposed, "debug_layer: residual only with Conv1d");
+    PackedLayer Lr;
+    rc = transposed ? pack_convT(Lr, w_host, bias_host, Cin, Cout, k, s) : pack_conv(Lr, w_host, bias_host, Cout, Cin, k, dil_or_stride);
+    if (rc != VO2W_OK) return rc;
+    rc = upload_layer(Lr);
+    if (rc != VO2W_OK) return rc;
+    const int Cin_p = Lr.Cin, Cout_p = (Cout + 15) / 16 * 16;
+    const long long Lp = vo2w_padded_len(L);
+    __nv_bfloat16* xin = nullptr;
+    float *of = nullptr, *rf = nullptr;
+    const size_t in_b = (size_t)B * Cin_p * Lp * 2, out_b = (size_t)B * Cout_p * Lo * 4;
+    VO2W_CUDA_OK(cudaMalloc(&xin, in_b));
+    VO2W_CUDA_OK(cudaMalloc(&of, out_b));
+    VO2W_CUDA_OK(cudaMemsetAsync(xin, 0, in_b, st));
+    rc = pack_ncl_to_operand(x_dev, xin, B, Cin, L, (int)Lp, in_slope, st);
+    EpilogueSpec ep;
+    ep.out_f32 = of;
+    if (rc == VO2W_OK && res_dev) {
+        VO2W_CUDA_OK(cudaMalloc(&rf, out_b));
+        rc = chunk_f32(res_dev, rf, B, Cout, Cout_p, (int)Lo, st);
+        ep.res[0] = rf;
+        ep.n_res = 1;
+    }
+    // the packed layer reports padded Cout through n_cols*n_tiles; the epilogue indexes by the true Cout rounded to 16
+    Lr.Cout = transposed ? Cout : Cout_p;
+    const PackedLayer* Ls[1] = {&Lr};
+    const __nv_bfloat16* ins[1] = {xin};
+    if (rc == VO2W_OK) rc = launch_layers(Ls, ins, 1, B, L, ep, st);
+    if (rc == VO2W_OK) rc = unchunk_f32(of, out_dev, B, Cout_p, Cout, (int)Lo, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (rc == VO2W_OK && e != cudaSuccess) {
+        vo2w_set_error("debug_layer: kernel failed: %s", cudaGetErrorString(e));
+        rc = VO2W_E_CUDA;
+    }
+    cudaFree(xin);
+    cudaFree(of);
+    if (rf) cudaFree(rf);
+    free_layer(Lr);
+    return rc;
+}
