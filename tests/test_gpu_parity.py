@@ -1,0 +1,257 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the oracle, the fixtures
+made from the reference, and size-independent properties at BASELINE sizes.  Run on the B200 box."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import visual_onoma_to_wave_b200 as v
+from visual_onoma_to_wave_b200 import _lib
+from visual_onoma_to_wave_b200.sharding import shard_bounds
+from visual_onoma_to_wave_b200.synthetic import V1_CONFIG, seeded_state_dict, synthetic_mel, synthetic_durations
+from oracle import hifigan_oracle as ho
+from oracle import length_regulator_oracle as lro
+from oracle.emulate import snr_db
+
+from helpers import lr_cases, check_lr_output
+
+pytestmark = pytest.mark.gpu
+
+MAX_ABS_ERR_FP32 = 1e-4     # north_star: fp32/TF32 mode
+MIN_SNR_DB_BF16 = 40.0      # north_star: bf16-input / fp32-accumulate mode (total-power SNR)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    assert _lib.lib().vo2w_device_check() == 0, "libvo2w needs an sm_100 device"
+    return torch.device("cuda:0")
+
+
+def make_gen(sd, precision, dev):
+    g = v.Generator(v.AttrDict(V1_CONFIG), precision=precision)
+    if any(k.endswith("weight_g") for k in sd):
+        g.load_state_dict(sd)
+        g.eval()
+        g.remove_weight_norm()
+    else:
+        g.eval()
+        g.remove_weight_norm()
+        g.load_state_dict(sd)
+    return g.to(dev)
+
+
+@pytest.fixture(scope="module")
+def gens(dev):
+    sd = seeded_state_dict(1234)
+    return {p: make_gen(sd, p, dev) for p in ("fp32", "bf16")}, sd
+
+
+# ------------------------------------------------------------------------------------------
+# LengthRegulator: bit-exact
+# ------------------------------------------------------------------------------------------
+def test_length_regulator_golden_bit_exact(dev, golden_dir):
+    g = np.load(os.path.join(golden_dir, "length_regulator.npz"))
+    lr = v.LengthRegulator()
+    n = 0
+    for name, x, dur, ml in lr_cases(g):
+        out, mel_len = lr(x.to(dev), torch.from_numpy(dur).to(dev), ml)
+        assert mel_len.dtype == torch.int64 and mel_len.is_cuda
+        check_lr_output(g, name, out.cpu(), mel_len.cpu().numpy())
+        if f"{name}.mask" in g.files:
+            m = v.get_mask_from_lengths(mel_len)
+            np.testing.assert_array_equal(m.cpu().numpy(), g[f"{name}.mask"])
+            out2, ml2, m2 = lr.LR(x.to(dev), torch.from_numpy(dur).to(dev), ml, return_mask=True)
+            assert torch.equal(out2, out) and torch.equal(ml2, mel_len)
+            if ml is None:
+                assert torch.equal(m2, m)
+        n += 1
+    assert n == 11
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_length_regulator_random_vs_oracle(dev, seed):
+    rng = np.random.default_rng(seed)
+    B, T, H = int(rng.integers(1, 9)), int(rng.integers(1, 70)), int(rng.choice([1, 3, 8, 80, 256]))
+    dt = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int32, torch.uint8][seed % 6]
+    x = torch.from_numpy(rng.standard_normal((B, T, H))).to(dt) if dt.is_floating_point else \
+        torch.from_numpy(rng.integers(0, 100, (B, T, H))).to(dt)
+    kind = seed % 4
+    if kind == 0:
+        dur = torch.from_numpy(rng.integers(-2, 9, (B, T)))
+    elif kind == 1:
+        dur = torch.from_numpy(rng.uniform(-2, 6, (B, T))).float()
+    elif kind == 2:
+        dur = torch.from_numpy(rng.integers(0, 4, (B, T))).to(torch.int32)
+    else:
+        dur = torch.from_numpy(rng.uniform(-1, 3, (B, T)))
+    total = int(lro.expand_counts(dur.numpy()).sum(1).max())
+    for ml in (None, max(1, total // 2), total + 5):
+        out, mel_len = v.LengthRegulator()(x.to(dev), dur.to(dev), ml)
+        raw = x.contiguous().view(torch.uint8).reshape(B, T, -1).numpy()
+        eo, eml = lro.length_regulate(raw, dur.numpy(), ml)
+        got = out.cpu().contiguous().view(torch.uint8).reshape(B, out.shape[1], -1).numpy()
+        assert got.shape == eo.shape and (got == eo).all()
+        np.testing.assert_array_equal(mel_len.cpu().numpy(), eml)
+
+
+def test_length_regulator_config3_and_bandwidth_shape(dev):
+    """config 3 (B=64, T_src=32, H=256) + a working set far larger than L2; checked by properties."""
+    x = torch.randn(64, 32, 256, generator=torch.Generator().manual_seed(0))
+    d = synthetic_durations(64, 32, seed=0)
+    out, ml = v.LengthRegulator()(x.to(dev), d.to(dev), None)
+    eo, eml = lro.length_regulate(x.numpy(), d.numpy(), None)
+    assert out.cpu().numpy().tobytes() == eo.tobytes() and (ml.cpu().numpy() == eml).all()
+    # large: B=1024, T_src=64 -> ~0.8 GB of output; every frame must equal its source token, tails zero
+    B, T, H = 1024, 64, 256
+    xd = torch.randn(B, T, H, device=dev)
+    dd = torch.randint(0, 25, (B, T), device=dev)
+    out, ml = v.LengthRegulator()(xd, dd, None)
+    assert torch.equal(ml, dd.sum(1)) and out.shape[1] == int(ml.max())
+    idx = torch.repeat_interleave(torch.arange(T, device=dev).repeat(B), dd.reshape(-1))
+    rows = torch.repeat_interleave(torch.arange(B, device=dev), ml)
+    pos = torch.cat([torch.arange(int(n), device=dev) for n in ml.tolist()])
+    assert torch.equal(out[rows, pos], xd[rows, idx])
+    tail = torch.arange(out.shape[1], device=dev)[None, :] >= ml[:, None]
+    assert float(out[tail].abs().max()) == 0.0
+
+
+# ------------------------------------------------------------------------------------------
+# single layers (known-answer against torch, both kernel families)
+# ------------------------------------------------------------------------------------------
+LAYERS = [  # transposed, Cin, Cout, k, dil|stride, L, B, in_slope, residual
+    (0, 32, 32, 3, 1, 200, 2, 0.1, True), (0, 32, 32, 11, 5, 300, 1, 0.1, False), (0, 64, 64, 7, 3, 130, 2, 0.1, True),
+    (0, 128, 128, 11, 1, 256, 1, 0.1, True), (0, 256, 256, 11, 5, 129, 1, 0.1, True), (0, 256, 256, 3, 1, 1, 2, 1.0, False),
+    (0, 80, 512, 7, 1, 50, 2, 1.0, False), (0, 32, 1, 7, 1, 300, 2, 0.01, False),
+    (1, 512, 256, 16, 8, 40, 1, 0.1, False), (1, 256, 128, 16, 8, 140, 1, 0.1, False),
+    (1, 128, 64, 4, 2, 300, 2, 0.1, False), (1, 64, 32, 4, 2, 129, 1, 0.1, False),
+]
+
+
+@pytest.mark.parametrize("umma", [0, 1], ids=["simt", "umma"])
+@pytest.mark.parametrize("case", LAYERS, ids=lambda c: "-".join(str(i) for i in c))
+def test_single_layer_against_torch(dev, case, umma):
+    tr, Cin, Cout, k, ds, L, B, slope, use_res = case
+    g = torch.Generator().manual_seed(Cin * 31 + k)
+    w = torch.randn((Cin, Cout, k) if tr else (Cout, Cin, k), generator=g) / (Cin * k) ** 0.5
+    b = torch.randn(Cout, generator=g) * 0.1
+    x = torch.randn(B, Cin, L, generator=g)
+    res = torch.randn(B, Cout, L, generator=g) if use_res else None
+    out = torch.full((B, Cout, L * (ds if tr else 1)), float("nan"), device=dev)
+    xd = x.to(dev)
+    rd = res.to(dev) if use_res else None
+    _lib.check(_lib.lib().vo2w_debug_layer(tr, umma, w.data_ptr(), b.data_ptr(), Cin, Cout, k, ds, xd.data_ptr(), B, L,
+                                           slope, rd.data_ptr() if use_res else None, out.data_ptr(), None))
+    xa = F.leaky_relu(x, slope) if slope != 1.0 else x
+    wr = w
+    if umma:      # tensor-core path rounds both operands to bf16, accumulates in fp32
+        xa, wr = xa.to(torch.bfloat16).float(), w.to(torch.bfloat16).float()
+    if tr:
+        ref = F.conv_transpose1d(xa.double(), wr.double(), b.double(), stride=ds, padding=ds // 2)
+    else:
+        ref = F.conv1d(xa.double(), wr.double(), b.double(), padding=ds * (k - 1) // 2, dilation=ds)
+    if use_res:
+        ref = ref + res.double()
+    err = float((out.cpu().double() - ref).abs().max())
+    assert err < 3e-5, err
+
+
+# ------------------------------------------------------------------------------------------
+# whole Generator
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", ["a", "b", "c"])
+def test_generator_against_reference_golden(dev, gens, golden_dir, case):
+    gen, _ = gens
+    g = np.load(os.path.join(golden_dir, f"generator_{case}.npz"))
+    mel = torch.from_numpy(g["mel"]).to(dev)
+    ref = torch.from_numpy(g["wav"])
+    wav32 = gen["fp32"](mel).cpu()
+    assert wav32.shape == ref.shape
+    assert float((wav32 - ref).abs().max()) <= MAX_ABS_ERR_FP32
+    wav16 = gen["bf16"](mel).cpu()
+    assert snr_db(ref, wav16) >= MIN_SNR_DB_BF16
+
+
+@pytest.mark.parametrize("kind", ["logmel", "randn"])
+def test_generator_against_oracle_config2_shape(dev, gens, kind):
+    """T=172 (2 s) as in config 2, B=2 so the CPU oracle finishes in seconds."""
+    gen, sd = gens
+    mel = synthetic_mel(2, 172, seed=0, kind=kind)
+    ref = ho.generator_forward(sd, mel)
+    wav32 = gen["fp32"](mel.to(dev)).cpu()
+    assert float((wav32 - ref).abs().max()) <= MAX_ABS_ERR_FP32
+    wav16 = gen["bf16"](mel.to(dev)).cpu()
+    assert snr_db(ref, wav16) >= MIN_SNR_DB_BF16
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_generator_batch_and_shard_invariance(dev, gens, precision):
+    """config 4's sharding property: per-utterance results do not depend on batch neighbours or on the
+    shard an utterance lands in (bit-equal), so N sequential shards == the unsharded run."""
+    gen, _ = gens
+    g = gen[precision]
+    mel = synthetic_mel(12, 64, seed=3).to(dev)
+    full = g(mel)
+    for ws in (2, 4, 8):
+        parts = [g(mel[slice(*shard_bounds(12, ws, r))].contiguous()) for r in range(ws) if shard_bounds(12, ws, r)[0] < shard_bounds(12, ws, r)[1]]
+        assert torch.equal(torch.cat(parts), full)
+    assert torch.equal(g(mel), full)                    # idempotent: workspace reuse leaves no state behind
+
+
+def test_generator_long_form_tiles_consistently(dev, gens):
+    """config 5 (30 s, T=2584): a long utterance must equal the same frames computed inside a longer
+    zero-extended context wherever the receptive field allows -- exercises dilation halos across tiles."""
+    gen, sd = gens
+    g = gen["bf16"]
+    mel = synthetic_mel(1, 2584, seed=5).to(dev)
+    wav = g(mel)
+    assert wav.shape == (1, 1, 2584 * 256) and bool(torch.isfinite(wav).all())
+    head = g(mel[:, :, :300].contiguous())
+    # samples further than the receptive field from the cut are identical
+    assert torch.equal(head[:, :, : 200 * 256], wav[:, :, : 200 * 256])
+    ref = ho.generator_forward(sd, mel[:, :, :300].cpu())
+    assert snr_db(ref, head.cpu()) >= MIN_SNR_DB_BF16
+
+
+def test_weight_norm_checkpoint_and_vocoder_infer_golden(dev, golden_dir):
+    g = np.load(os.path.join(golden_dir, "vocoder_infer_wn.npz"))
+    sd = seeded_state_dict(4321, weight_norm=True)
+    for k in sd:
+        if k.endswith("weight_g"):
+            sd[k] = sd[k] * (1.0 + 0.25 * torch.sin(torch.arange(sd[k].numel()).float()).reshape(sd[k].shape))
+    mel = torch.from_numpy(g["mel"])
+    lengths = g["lengths"].tolist()
+    cfg = {"vocoder": {"model": "HiFi-GAN"}}
+    voc = make_gen(sd, "fp32", dev)
+    for m in (mel.to(dev), mel):                        # device mels (reference flow) and host mels (host-buffer ABI)
+        wavs = v.vocoder_infer(m, voc, cfg, {}, lengths=lengths, Normalize=False)
+        assert [w.shape for w in wavs] == [g["wav0"].shape, g["wav1"].shape] and wavs[0].dtype == np.float32
+        assert np.abs(wavs[0] - g["wav0"]).max() <= MAX_ABS_ERR_FP32
+        assert np.abs(wavs[1] - g["wav1"]).max() <= MAX_ABS_ERR_FP32
+    voc16 = make_gen(sd, "bf16", dev)
+    wavs = v.vocoder_infer(mel, voc16, cfg, {}, lengths=lengths, Normalize=False)
+    ref = torch.from_numpy(np.concatenate([g["wav0"], g["wav1"]]))
+    assert snr_db(ref, torch.from_numpy(np.concatenate(wavs))) >= MIN_SNR_DB_BF16
+    # int16 output (utils/model.py:83-86) with a config that has the key path the reference reads
+    pc = {"preprocessing": {"audio": {"max_wav_value": 32768.0}}}
+    i16_dev = v.vocoder_infer(mel.to(dev), voc, cfg, pc, lengths=lengths, Normalize=True)
+    i16_host = v.vocoder_infer(mel, voc, cfg, pc, lengths=lengths, Normalize=True)
+    assert i16_dev[0].dtype == np.int16 and i16_host[0].dtype == np.int16
+    for a, b in zip(i16_dev, i16_host):
+        np.testing.assert_array_equal(a, b)
+    np.testing.assert_allclose(i16_dev[0], (g["wav0"] * 32768.0).astype("int16"), atol=4)
+
+
+def test_error_conventions(dev, gens):
+    gen, _ = gens
+    with pytest.raises(RuntimeError):
+        gen["bf16"](torch.zeros(1, 81, 4, device=dev))
+    with pytest.raises(RuntimeError):
+        gen["bf16"](torch.zeros(1, 80, 4, device=dev, dtype=torch.float16))
+    with pytest.raises(RuntimeError):
+        v.LengthRegulator()(torch.zeros(2, 3, 4, device=dev), torch.ones(2, 4, device=dev), None)
+    lib = _lib.lib()
+    assert lib.vo2w_generator_forward(None, None, 1, 1, None, None, 0, 0, None) == _lib.E_INVALID
