@@ -81,3 +81,45 @@ def snr_db(ref: torch.Tensor, got: torch.Tensor) -> float:
     ref = ref.double()
     err = got.double() - ref
     return float(10 * torch.log10(ref.pow(2).sum() / err.pow(2).sum().clamp_min(1e-300)))
+
+
+def generator_forward_emulated_v2(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float32, taps=None):
+    """Dataflow of the pair-fused bf16 pipeline (DESIGN.md "Numerics"): every activation tensor
+    that reaches HBM is raw bf16; leaky-relu is applied to the bf16 value and rounded to bf16 again
+    for the MMA operand; conv1->conv2 intermediate is bf16(lrelu(fp32)); residual adds, bias and the
+    MRF sum are fp32; the MRF average is stored as raw bf16."""
+    sd = fold_weight_norm(sd)
+    W = {k: (_r(v.float(), "bf16") if k.endswith("weight") else v.float()).to(acc_dtype) for k, v in sd.items()}
+    nk = len(cfg["resblock_kernel_sizes"])
+    f32 = lambda t: t.float().to(acc_dtype)
+    b16 = lambda t: _r(t, "bf16")
+    act = lambda t, s: b16(F.leaky_relu(t, s))          # bf16 in, bf16 out
+
+    with torch.no_grad():
+        x = b16(f32(F.conv1d(b16(mel.to(acc_dtype)), W["conv_pre.weight"], W["conv_pre.bias"], padding=3)))
+        if taps is not None:
+            taps["conv_pre"] = x.float()
+        for i, (u, k) in enumerate(zip(cfg["upsample_rates"], cfg["upsample_kernel_sizes"])):
+            x = b16(f32(F.conv_transpose1d(act(x, LRELU_SLOPE), W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u,
+                                           padding=(k - u) // 2)))
+            if taps is not None:
+                taps[f"ups.{i}"] = x.float()
+            xs = None
+            for j, (rk, rd) in enumerate(zip(cfg["resblock_kernel_sizes"], cfg["resblock_dilation_sizes"])):
+                p = f"resblocks.{i * nk + j}"
+                r = x
+                for m, d in enumerate(rd):
+                    t = f32(F.conv1d(act(r, LRELU_SLOPE), W[f"{p}.convs1.{m}.weight"], W[f"{p}.convs1.{m}.bias"],
+                                     padding=get_padding(rk, d), dilation=d))
+                    t = b16(F.leaky_relu(t, LRELU_SLOPE))
+                    y = f32(F.conv1d(t, W[f"{p}.convs2.{m}.weight"], W[f"{p}.convs2.{m}.bias"], padding=get_padding(rk, 1)))
+                    r = f32(y + r)
+                    if m < 2:
+                        r = b16(r)
+                xs = r if xs is None else f32(xs + r)
+            x = b16(f32(xs / nk))
+            if taps is not None:
+                taps[f"mrf.{i}"] = x.float()
+        x = f32(F.conv1d(act(x, 0.01), W["conv_post.weight"], W["conv_post.bias"], padding=3))
+        x = torch.tanh(x)
+    return x.float()
