@@ -79,8 +79,10 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
+        // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues ==========
+        // (a lane-0 branch makes ptxas wrap every tcgen05.mma in a per-lane uniformisation loop, which
+        //  roughly doubles the issue cost; profiles/r01_umma_issue_rates.txt)
+        {
             int it = 0;
             // transposed conv: phases r >= s/2 read x[q+1], x[q] instead of x[q], x[q-1]
             const uint32_t extra_shift = p.up_s > 1 ? (uint32_t)((ty * p.phases_per_tile + p.up_pad) / p.up_s) : 0u;
@@ -99,21 +101,26 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
                         const uint32_t round = (uint32_t)(it / UMMA_STAGES);
                         mbar_wait(full_bar(stage), round & 1u);
                         tc_fence_after();
-                        const uint32_t bs = b_smem + (uint32_t)stage * p.stage_bytes;
-                        for (int st = 0; st < p.kb_steps; ++st) {
-                            const uint32_t kstep = (uint32_t)(kb * p.kb_steps + st);
-                            const uint32_t a_addr = a_smem + (kstep * 2u * (uint32_t)sg.rows + (uint32_t)item.row_shift + extra_shift) * 16u;
-                            const uint32_t b_addr = bs + (uint32_t)st * 2u * b_lbo;
-                            const uint32_t accumulate = (item.zero_init && kb == 0 && st == 0) ? 0u : 1u;
-                            umma_bf16(d_tmem, umma_smem_desc(a_addr, a_lbo, 128u), umma_smem_desc(b_addr, b_lbo, 128u),
-                                      idesc, accumulate);
+                        if (elect_one_sync()) {
+                            const uint32_t bs = b_smem + (uint32_t)stage * p.stage_bytes;
+                            for (int st = 0; st < p.kb_steps; ++st) {
+                                const uint32_t kstep = (uint32_t)(kb * p.kb_steps + st);
+                                const uint32_t a_addr = a_smem + (kstep * 2u * (uint32_t)sg.rows + (uint32_t)item.row_shift + extra_shift) * 16u;
+                                const uint32_t b_addr = bs + (uint32_t)st * 2u * b_lbo;
+                                const uint32_t accumulate = (item.zero_init && kb == 0 && st == 0) ? 0u : 1u;
+                                umma_bf16(d_tmem, umma_smem_desc(a_addr, a_lbo, 128u), umma_smem_desc(b_addr, b_lbo, 128u),
+                                          idesc, accumulate);
+                            }
+                            umma_commit(empty_bar(stage));   // stage reusable once these MMAs retire
                         }
-                        umma_commit(empty_bar(stage));   // stage reusable once these MMAs retire
+                        __syncwarp();
                     }
                 }
-                umma_commit(a_empty);                    // input tile reusable
+                if (elect_one_sync()) umma_commit(a_empty);  // input tile reusable
+                __syncwarp();
             }
-            umma_commit(acc_full);
+            if (elect_one_sync()) umma_commit(acc_full);
+            __syncwarp();
         }
     } else {
         // ===================== epilogue: TMEM -> registers -> global =====================
@@ -167,13 +174,22 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
                 *(float4*)(p.out_f32 + f_off) = make_float4(v[0], v[1], v[2], v[3]);
                 *(float4*)(p.out_f32 + f_off + f_step) = make_float4(v[4], v[5], v[6], v[7]);
             }
-            if (p.out_bf16) {
+            if (p.out_bf16 || p.out_raw) {
+                // HBM stream format of the bf16 mode: raw value rounded to bf16; the next layer's operand is
+                // leaky-relu of that ROUNDED value (what a consumer reading the stream would compute)
                 __nv_bfloat162 h[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    h[i] = __floats2bfloat162_rn(lrelu(v[2 * i], p.out_slope), lrelu(v[2 * i + 1], p.out_slope));
                 const size_t o = (((size_t)b * (p.Cout >> 3) + (co >> 3)) * p.Lp_out + VO2W_PAD_ROWS + lo) * 8;
-                *(uint4*)(p.out_bf16 + o) = *(const uint4*)h;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                if (p.out_raw) *(uint4*)(p.out_raw + o) = *(const uint4*)h;
+                if (p.out_bf16) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 f = __bfloat1622float2(h[i]);
+                        h[i] = __floats2bfloat162_rn(lrelu(f.x, p.out_slope), lrelu(f.y, p.out_slope));
+                    }
+                    *(uint4*)(p.out_bf16 + o) = *(const uint4*)h;
+                }
             }
             }   // !out_wave
             }   // valid

@@ -2,8 +2,10 @@
 //
 // Replaces hifigan.Generator (scripts/hifigan/models.py:112-174) behind the C ABI of
 // include/vo2w.h.  Two precision modes share this schedule:
-//   VO2W_PREC_BF16  tcgen05 implicit-GEMM kernels (conv_umma.cu) on chunked bf16 operand
-//                   buffers with an fp32 residual stream;
+//   VO2W_PREC_BF16  tcgen05 kernels on chunked bf16 operand buffers: every ResBlock iteration
+//                   (conv1 -> lrelu -> conv2 -> +x) is ONE fused launch (pair_umma.cu), conv_pre /
+//                   upsamplers / conv_post are single-conv launches (conv_umma.cu); activations
+//                   travel through HBM as bf16, the MRF sum as fp32;
 //   VO2W_PREC_FP32  CUDA-core fp32 kernels (conv_simt.cu) on plain NCL tensors.
 #include <map>
 #include <string>
@@ -11,6 +13,7 @@
 
 #include "conv_simt.cuh"
 #include "pack.cuh"
+#include "pair_umma.cuh"
 
 namespace {
 
@@ -22,15 +25,14 @@ struct LayerW {            // one reference layer inside the fp32 blob
 struct StageBufs {         // per upsampling stage, offsets in bytes into the workspace
     int C = 0;
     long long L = 0, Lp = 0;
-    size_t x_f32 = 0;              // ups output, fp32 (residual for the first conv pair)
-    size_t xa = 0;                 // bf16 leaky-relu(x)
-    size_t xr[3] = {0, 0, 0};      // fp32 residual stream of ResBlock j
-    size_t ya[3] = {0, 0, 0};      // bf16 leaky-relu(residual stream)
-    size_t t[3] = {0, 0, 0};       // bf16 leaky-relu(conv1 output)
-    size_t mrf = 0;                // bf16 leaky-relu(MRF average) = operand of the next layer
-    size_t mrf_f32 = 0;            // debug tap only
+    // bf16 mode: operand-layout buffers [B][C/8][Lp][8]
+    size_t x = 0, xa = 0;          // ups output: raw stream value, leaky-relu(0.1) of it
+    size_t r[2] = {0, 0};          // ResBlock stream after iteration 0 / 1 (raw)
+    size_t ra[2] = {0, 0};         // leaky-relu(0.1) of it
+    size_t S = 0;                  // fp32 [B][C/4][L][4]: running sum over the ResBlocks of the stage
+    size_t mrf = 0;                // leaky-relu(xs / num_kernels) = operand of the next layer
     // fp32 mode (NCL)
-    size_t r = 0, tt = 0, xs = 0;
+    size_t x_f32 = 0, rr = 0, tt = 0, xs = 0;
 };
 
 struct Plan {
@@ -52,8 +54,8 @@ struct vo2w_generator {
     float* w_dev = nullptr;        // fp32 blob on the device (fp32 mode + biases)
     // bf16 mode
     PackedLayer conv_pre, conv_post, ups[4];
-    PackedLayer c1[12][3], c2[12][3];
-    float* mrf_bias[4] = {nullptr, nullptr, nullptr, nullptr};   // sum of the three convs2[2] biases
+    PackedPair pairs[12][3];       // resblocks[n] iteration m: convs1[m] + convs2[m]
+    int pair_cg = 2;               // CTAs per tcgen05 group of the fused kernel
     // last forward (debug taps, launch count)
     Plan last;
     void* last_ws = nullptr;
@@ -87,23 +89,21 @@ Plan make_plan(const vo2w_generator* g, int B, int T) {
         const long long Lp0 = vo2w_padded_len(T);
         p.melb = take((size_t)B * 80 * Lp0 * 2);
         p.a0 = take((size_t)B * C0 * Lp0 * 2);
-        if (g->debug_taps) p.c0_f32 = take((size_t)B * C0 * T * 4);
         for (int i = 0; i < g->n_stage; ++i) {
             StageBufs& s = p.st[i];
             L *= g->cfg.upsample_rates[i];
             s.C = stage_channels(g, i);
             s.L = L;
             s.Lp = vo2w_padded_len(L);
-            const size_t f32b = (size_t)B * s.C * L * 4, bfb = (size_t)B * s.C * s.Lp * 2;
-            s.x_f32 = take(f32b);
+            const size_t bfb = (size_t)B * s.C * s.Lp * 2;
+            s.x = take(bfb);
             s.xa = take(bfb);
-            for (int j = 0; j < g->nk; ++j) {
-                s.xr[j] = take(f32b);
-                s.ya[j] = take(bfb);
-                s.t[j] = take(bfb);
+            for (int m = 0; m < 2; ++m) {
+                s.r[m] = take(bfb);
+                s.ra[m] = take(bfb);
             }
+            s.S = take((size_t)B * s.C * L * 4);
             s.mrf = take(bfb);
-            if (g->debug_taps) s.mrf_f32 = take(f32b);
         }
     } else {
         p.c0_f32 = take((size_t)B * C0 * T * 4);
@@ -114,7 +114,7 @@ Plan make_plan(const vo2w_generator* g, int B, int T) {
             s.L = L;
             const size_t f32b = (size_t)B * s.C * L * 4;
             s.x_f32 = take(f32b);
-            s.r = take(f32b);
+            s.rr = take(f32b);
             s.tt = take(f32b);
             s.xs = take(f32b);
         }
@@ -190,26 +190,21 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
         };
         VO2W_TRY(pc(g->conv_pre, idx_conv_pre(), 1));
         VO2W_TRY(pc(g->conv_post, idx_conv_post(g), 1));
+        const char* cge = getenv("VO2W_PAIR_CG");
+        g->pair_cg = (cge && cge[0] == '1') ? 1 : 2;
         for (int i = 0; i < g->n_stage; ++i) {
             const LayerW& l = g->lw[idx_ups(i)];
             VO2W_TRY(pack_convT(g->ups[i], W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, cfg->upsample_rates[i]));
             VO2W_TRY(upload_layer(g->ups[i]));
             const int ch = stage_channels(g, i);
-            std::vector<float> bsum(ch, 0.f);
             for (int j = 0; j < g->nk; ++j) {
                 const int n = i * g->nk + j;
                 for (int m = 0; m < 3; ++m) {
-                    VO2W_TRY(pc(g->c1[n][m], idx_rb(g, n, 0, m), cfg->resblock_dilation_sizes[j][m]));
-                    VO2W_TRY(pc(g->c2[n][m], idx_rb(g, n, 1, m), 1));
+                    const LayerW& l1 = g->lw[idx_rb(g, n, 0, m)];
+                    const LayerW& l2 = g->lw[idx_rb(g, n, 1, m)];
+                    VO2W_TRY(pack_pair(g->pairs[n][m], W + l1.w_off, W + l1.b_off, W + l2.w_off, W + l2.b_off, ch,
+                                       cfg->resblock_kernel_sizes[j], cfg->resblock_dilation_sizes[j][m], g->pair_cg));
                 }
-                const float* b = W + g->lw[idx_rb(g, n, 1, 2)].b_off;
-                for (int c = 0; c < ch; ++c) bsum[c] += b[c];
-            }
-            if (cudaMalloc(&g->mrf_bias[i], ch * 4) != cudaSuccess ||
-                cudaMemcpy(g->mrf_bias[i], bsum.data(), ch * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
-                vo2w_set_error("generator_create: uploading bias failed");
-                vo2w_generator_destroy(g);
-                return VO2W_E_CUDA;
             }
         }
     }
@@ -223,15 +218,9 @@ extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
     if (g->w_dev) cudaFree(g->w_dev);
     free_layer(g->conv_pre);
     free_layer(g->conv_post);
-    for (int i = 0; i < 4; ++i) {
-        free_layer(g->ups[i]);
-        if (g->mrf_bias[i]) cudaFree(g->mrf_bias[i]);
-    }
+    for (int i = 0; i < 4; ++i) free_layer(g->ups[i]);
     for (int n = 0; n < 12; ++n)
-        for (int m = 0; m < 3; ++m) {
-            free_layer(g->c1[n][m]);
-            free_layer(g->c2[n][m]);
-        }
+        for (int m = 0; m < 3; ++m) free_pair(g->pairs[n][m]);
     delete g;
     return VO2W_OK;
 }
@@ -258,70 +247,51 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
 
     // mel [B,80,T] fp32 -> operand buffer
     VO2W_RUN(pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
-    {   // x = conv_pre(mel); next consumer is leaky_relu(0.1) -> ups[0]
+    {   // x = conv_pre(mel); the only consumer is leaky_relu(0.1) -> ups[0]
         const PackedLayer* L[1] = {&g->conv_pre};
         const __nv_bfloat16* in[1] = {bf(p.melb)};
         EpilogueSpec ep;
         ep.out_bf16 = bf(p.a0);
         ep.out_slope = 0.1f;
-        if (g->debug_taps) ep.out_f32 = f32(p.c0_f32);
         VO2W_RUN(launch_layers(L, in, 1, B, T, ep, st));
     }
     const __nv_bfloat16* stage_in = bf(p.a0);
     long long L_in = T;
     for (int i = 0; i < g->n_stage; ++i) {
         const StageBufs& s = p.st[i];
-        {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM, writes fp32 x and bf16 leaky_relu(x)
+        {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM; writes the stream x and leaky_relu(x), both bf16
             const PackedLayer* L[1] = {&g->ups[i]};
             const __nv_bfloat16* in[1] = {stage_in};
             EpilogueSpec ep;
-            ep.out_f32 = f32(s.x_f32);
+            ep.out_raw = bf(s.x);
             ep.out_bf16 = bf(s.xa);
             ep.out_slope = 0.1f;
             VO2W_RUN(launch_layers(L, in, 1, B, (int)L_in, ep, st));
         }
-        for (int m = 0; m < 3; ++m) {
-            for (int j = 0; j < g->nk; ++j) {   // xt = c1(leaky_relu(x)); operand of c2 is leaky_relu(xt)
-                const int n = i * g->nk + j;
-                const PackedLayer* L[1] = {&g->c1[n][m]};
-                const __nv_bfloat16* in[1] = {m == 0 ? bf(s.xa) : bf(s.ya[j])};
-                EpilogueSpec ep;
-                ep.out_bf16 = bf(s.t[j]);
-                ep.out_slope = 0.1f;
-                VO2W_RUN(launch_layers(L, in, 1, B, (int)s.L, ep, st));
-            }
-            if (m < 2) {
-                for (int j = 0; j < g->nk; ++j) {   // x = c2(leaky_relu(xt)) + x
-                    const int n = i * g->nk + j;
-                    const PackedLayer* L[1] = {&g->c2[n][m]};
-                    const __nv_bfloat16* in[1] = {bf(s.t[j])};
-                    EpilogueSpec ep;
-                    ep.res[0] = m == 0 ? f32(s.x_f32) : f32(s.xr[j]);
-                    ep.n_res = 1;
-                    ep.out_f32 = f32(s.xr[j]);
-                    ep.out_bf16 = bf(s.ya[j]);
-                    ep.out_slope = 0.1f;
-                    VO2W_RUN(launch_layers(L, in, 1, B, (int)s.L, ep, st));
+        // F.leaky_relu(x) before conv_post uses the default slope 0.01 (models.py:161)
+        const float next_slope = i + 1 < g->n_stage ? 0.1f : 0.01f;
+        for (int j = 0; j < g->nk; ++j) {
+            const int n = i * g->nk + j;
+            for (int m = 0; m < 3; ++m) {   // one ResBlock iteration per launch (models.py:97-103)
+                PairIO io;
+                io.xa = m == 0 ? bf(s.xa) : bf(s.ra[m - 1]);
+                io.x = m == 0 ? bf(s.x) : bf(s.r[m - 1]);
+                if (m < 2) {
+                    io.mode = PAIR_OUT_STREAM;
+                    io.out_raw = bf(s.r[m]);
+                    io.out_act = bf(s.ra[m]);
+                    io.out_slope = 0.1f;
+                } else {
+                    // xs = sum_j resblocks[j](x); x = xs / num_kernels (models.py:154-160): fp32 running sum,
+                    // the last ResBlock of the stage writes the next layer's operand
+                    io.S = f32(s.S);
+                    io.mode = g->nk == 1 ? PAIR_OUT_SUM_ONLY
+                              : (j == 0 ? PAIR_OUT_SUM_FIRST : (j == g->nk - 1 ? PAIR_OUT_SUM_LAST : PAIR_OUT_SUM_ADD));
+                    io.out_act = bf(s.mrf);
+                    io.out_slope = next_slope;
+                    io.inv_div = 1.0f / (float)g->nk;
                 }
-            } else {
-                // last conv of all ResBlocks of the stage in ONE launch: the three c2 accumulate into
-                // the same TMEM tile; epilogue adds the three residual streams and divides by
-                // num_kernels (xs = sum_j resblock_j(x); x = xs / num_kernels, models.py:154-160).
-                const PackedLayer* L[3];
-                const __nv_bfloat16* in[3];
-                EpilogueSpec ep;
-                for (int j = 0; j < g->nk; ++j) {
-                    L[j] = &g->c2[i * g->nk + j][2];
-                    in[j] = bf(s.t[j]);
-                    ep.res[j] = f32(s.xr[j]);
-                }
-                ep.n_res = g->nk;
-                ep.bias = g->mrf_bias[i];
-                ep.div = (float)g->nk;
-                ep.out_bf16 = bf(s.mrf);
-                ep.out_slope = i + 1 < g->n_stage ? 0.1f : 0.01f;   // F.leaky_relu(x) default slope before conv_post
-                if (g->debug_taps) ep.out_f32 = f32(s.mrf_f32);
-                VO2W_RUN(launch_layers(L, in, g->nk, B, (int)s.L, ep, st));
+                VO2W_RUN(pair_launch(g->pairs[n][m], io, B, (int)s.L, st));
             }
         }
         stage_in = bf(s.mrf);
@@ -373,7 +343,7 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             const int k = g->cfg.resblock_kernel_sizes[j];
             for (int m = 0; m < 3; ++m) {
                 const int d = g->cfg.resblock_dilation_sizes[j][m];
-                const float* xin = m == 0 ? f32(s.x_f32) : f32(s.r);
+                const float* xin = m == 0 ? f32(s.x_f32) : f32(s.rr);
                 SimtConv q = c;
                 int idx = idx_rb(g, n, 0, m);
                 q.x = xin; q.w = W(idx); q.bias = Bi(idx); q.out = f32(s.tt);
@@ -383,7 +353,7 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
                 q.x = f32(s.tt); q.w = W(idx); q.bias = Bi(idx); q.dil = 1; q.pad = (k - 1) / 2;
                 q.res = xin;
                 if (m < 2) {
-                    q.out = f32(s.r);
+                    q.out = f32(s.rr);
                 } else {            // xs (+)= resblock_j(x); after the last one x = xs / num_kernels
                     q.out = f32(s.xs);
                     q.accum = j == 0 ? 0 : 1;
@@ -477,22 +447,24 @@ extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap
     long long L = 0;
     bool found = false;
     const bool bf = g->precision == VO2W_PREC_BF16;
-    if (name == "conv_pre" && (!bf || g->debug_taps)) {
+    bool is_bf16_buf = false;
+    if (name == "conv_pre" && !bf) {
         off = p.c0_f32; C = g->cfg.upsample_initial_channel; L = p.T; found = true;
     }
     for (int i = 0; i < g->n_stage && !found; ++i) {
-        if (name == "ups." + std::to_string(i)) { off = p.st[i].x_f32; found = true; }
-        else if (name == "mrf." + std::to_string(i) && (!bf || g->debug_taps)) { off = bf ? p.st[i].mrf_f32 : p.st[i].xs; found = true; }
+        if (name == "ups." + std::to_string(i)) { off = bf ? p.st[i].x : p.st[i].x_f32; found = true; is_bf16_buf = bf; }
+        else if (name == "mrf." + std::to_string(i) && !bf) { off = p.st[i].xs; found = true; }
+        else if (name == "mrf_act." + std::to_string(i) && bf) { off = p.st[i].mrf; found = true; is_bf16_buf = true; }
         if (found) { C = p.st[i].C; L = p.st[i].L; }
     }
-    VO2W_REQUIRE(found, "debug_tap: unknown or disabled tap '%s' (set VO2W_DEBUG_TAPS=1 before create)", tap);
+    VO2W_REQUIRE(found, "debug_tap: unknown tap '%s' for this precision mode", tap);
     const size_t n = (size_t)p.B * C * L;
     VO2W_REQUIRE(n <= capacity, "debug_tap: need %zu floats, capacity %zu", n, capacity);
     VO2W_CUDA_OK(cudaDeviceSynchronize());
-    if (bf) {
+    if (is_bf16_buf) {
         float* tmp = nullptr;
         VO2W_CUDA_OK(cudaMalloc(&tmp, n * 4));
-        int rc = unchunk_f32((const float*)(ws + off), tmp, p.B, C, C, (int)L, 0);
+        int rc = unchunk_bf16((const __nv_bfloat16*)(ws + off), tmp, p.B, C, (int)L, (int)vo2w_padded_len(L), 0);
         if (rc == VO2W_OK && cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = VO2W_E_CUDA;
         cudaFree(tmp);
         if (rc != VO2W_OK) return rc;

@@ -399,12 +399,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                             } else {
                                 float* s0 = p.S + s_row + (size_t)(chunk * 2) * s_step;
                                 float* s1 = s0 + s_step;
-                                if (p.mode != PAIR_OUT_SUM_FIRST) {
+                                if (p.mode == PAIR_OUT_SUM_ADD || p.mode == PAIR_OUT_SUM_LAST) {
                                     const float4 a0 = *(const float4*)s0, a1 = *(const float4*)s1;
                                     v[0] += a0.x; v[1] += a0.y; v[2] += a0.z; v[3] += a0.w;
                                     v[4] += a1.x; v[5] += a1.y; v[6] += a1.z; v[7] += a1.w;
                                 }
-                                if (p.mode != PAIR_OUT_SUM_LAST) {
+                                if (p.mode == PAIR_OUT_SUM_FIRST || p.mode == PAIR_OUT_SUM_ADD) {
                                     *(float4*)s0 = make_float4(v[0], v[1], v[2], v[3]);
                                     *(float4*)s1 = make_float4(v[4], v[5], v[6], v[7]);
                                 } else {
@@ -548,8 +548,10 @@ int pair_launch(const PackedPair& P, const PairIO& io, int B, int L, cudaStream_
         attr_set = true;
     }
     VO2W_REQUIRE(io.xa && io.x, "pair_launch: null input");
-    VO2W_REQUIRE(io.mode == PAIR_OUT_STREAM ? (io.out_raw && io.out_act) : (io.S != nullptr), "pair_launch: missing output buffer");
-    VO2W_REQUIRE(io.mode != PAIR_OUT_SUM_LAST || io.out_act, "pair_launch: missing activation output");
+    VO2W_REQUIRE(io.mode >= PAIR_OUT_STREAM && io.mode <= PAIR_OUT_SUM_ONLY, "pair_launch: bad mode %d", io.mode);
+    VO2W_REQUIRE(io.mode != PAIR_OUT_STREAM || (io.out_raw && io.out_act), "pair_launch: missing stream output");
+    VO2W_REQUIRE(io.mode == PAIR_OUT_STREAM || io.mode == PAIR_OUT_SUM_ONLY || io.S, "pair_launch: missing sum buffer");
+    VO2W_REQUIRE((io.mode != PAIR_OUT_SUM_LAST && io.mode != PAIR_OUT_SUM_ONLY) || io.out_act, "pair_launch: missing activation output");
     PairP p;
     const int grid = pair_plan(p, P.C, P.k, P.dil, P.cg, B, L, n_sms);
     if (grid < 0) return grid;

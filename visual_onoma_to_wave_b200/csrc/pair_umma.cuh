@@ -15,6 +15,7 @@
 #define PAIR_OUT_STREAM 0         // out_raw = r (bf16), out_act = lrelu(r, out_slope) (bf16)
 #define PAIR_OUT_SUM_FIRST 1      // S  = r                      (fp32, first ResBlock of the MRF sum)
 #define PAIR_OUT_SUM_ADD 2        // S += r
+#define PAIR_OUT_SUM_ONLY 4       // out_act = lrelu(r * inv_div, out_slope)         (num_kernels == 1)
 #define PAIR_OUT_SUM_LAST 3       // out_act = lrelu((S + r) * inv_div, out_slope)   (x = xs / num_kernels, models.py:154-160)
 
 struct PairP {
