@@ -109,14 +109,18 @@ int vo2w_debug_layer(int transposed, int use_umma, const float* w_host, const fl
                      int Cout, int k, int dil_or_stride, const float* x_dev, int B, int L, float in_slope,
                      const float* res_dev, float* out_dev, void* stream);
 
-/* Known-answer probe of the fused ResBlock iteration (scripts/hifigan/models.py:97-103):
- *   out = x + conv2(leaky_relu(conv1(leaky_relu(x, 0.1)) , 0.1))   with conv1 = Conv1d(C,C,k,dilation=dil),
- *   conv2 = Conv1d(C,C,k), both "same"-padded; x/out NCL fp32 on the device.  The kernel keeps x in bf16
- *   (the HBM format of the bf16 mode), so `out` is the bf16-rounded stream value; act (optional) receives
- *   leaky_relu(out, 0.1).  cg = CTAs per tcgen05 group (1, or 2 for cta_group::2 pairs). */
-int vo2w_debug_pair(const float* w1_host, const float* b1_host, const float* w2_host, const float* b2_host,
-                    int C, int k, int dil, int cg, const float* x_dev, int B, int L, float* out_dev,
-                    float* act_dev, void* stream);
+/* Known-answer probe of the fused ResBlock-iteration kernel (scripts/hifigan/models.py:97-103, 154-160):
+ *   y   = scale * sum_{s < n_seg} [ x_s + conv2_s(leaky_relu(conv1_s(leaky_relu(x_s, 0.1)), 0.1)) ]
+ *   out = bf16(y)  (optional),  act = leaky_relu(out, out_slope)
+ * conv1_s = Conv1d(C,C,ks[s],dilation=dils[s]), conv2_s = Conv1d(C,C,ks[s]), both "same"-padded, weights and
+ * biases in the torch layout on the host (arrays of n_seg pointers); x_s / out / act NCL fp32 on the device.
+ * n_seg = 1, scale = 1 is one ResBlock iteration; n_seg = num_kernels, scale = 1/num_kernels the MRF
+ * average of a stage.  The kernel keeps x_s in bf16 (the HBM format of the bf16 mode).
+ * cg = CTAs per tcgen05 group (1, or 2 for cta_group::2 pairs). */
+int vo2w_debug_pair(int n_seg, const float* const* w1_host, const float* const* b1_host,
+                    const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
+                    const int* dils, int cg, const float* const* x_dev, int B, int L, float scale,
+                    float out_slope, float* out_dev, float* act_dev, void* stream);
 
 /* Host-only probe of the weight packing (no device needed): meta[0..11] = {Cin, Cout, n_cols,
  * n_tiles, phases_per_tile, halo_l, halo_r, n_items, w_tile_stride, up_s, w_elems, bias_elems},

@@ -4,8 +4,9 @@
 // include/vo2w.h.  Two precision modes share this schedule:
 //   VO2W_PREC_BF16  tcgen05 kernels on chunked bf16 operand buffers: every ResBlock iteration
 //                   (conv1 -> lrelu -> conv2 -> +x) is ONE fused launch (pair_umma.cu), conv_pre /
-//                   upsamplers / conv_post are single-conv launches (conv_umma.cu); activations
-//                   travel through HBM as bf16, the MRF sum as fp32;
+//                   upsamplers / conv_post are single-conv launches (conv_umma.cu); the last
+//                   iteration of all ResBlocks of a stage plus the MRF average is one launch too;
+//                   activations travel through HBM as bf16;
 //   VO2W_PREC_FP32  CUDA-core fp32 kernels (conv_simt.cu) on plain NCL tensors.
 #include <map>
 #include <string>
@@ -27,9 +28,8 @@ struct StageBufs {         // per upsampling stage, offsets in bytes into the wo
     long long L = 0, Lp = 0;
     // bf16 mode: operand-layout buffers [B][C/8][Lp][8]
     size_t x = 0, xa = 0;          // ups output: raw stream value, leaky-relu(0.1) of it
-    size_t r[2] = {0, 0};          // ResBlock stream after iteration 0 / 1 (raw)
-    size_t ra[2] = {0, 0};         // leaky-relu(0.1) of it
-    size_t S = 0;                  // fp32 [B][C/4][L][4]: running sum over the ResBlocks of the stage
+    size_t r[3][2] = {};           // stream of ResBlock j after iteration 0 / 1 (raw)
+    size_t ra[3][2] = {};          // leaky-relu(0.1) of it
     size_t mrf = 0;                // leaky-relu(xs / num_kernels) = operand of the next layer
     // fp32 mode (NCL)
     size_t x_f32 = 0, rr = 0, tt = 0, xs = 0;
@@ -55,6 +55,8 @@ struct vo2w_generator {
     // bf16 mode
     PackedLayer conv_pre, conv_post, ups[4];
     PackedPair pairs[12][3];       // resblocks[n] iteration m: convs1[m] + convs2[m]
+    PackedGroup iter_group[12][2]; // one launch = iteration m < 2 of resblocks[n]
+    PackedGroup mrf_group[4];      // one launch = last iteration of all ResBlocks of a stage + the MRF average
     int pair_cg = 2;               // CTAs per tcgen05 group of the fused kernel
     // last forward (debug taps, launch count)
     Plan last;
@@ -98,11 +100,11 @@ Plan make_plan(const vo2w_generator* g, int B, int T) {
             const size_t bfb = (size_t)B * s.C * s.Lp * 2;
             s.x = take(bfb);
             s.xa = take(bfb);
-            for (int m = 0; m < 2; ++m) {
-                s.r[m] = take(bfb);
-                s.ra[m] = take(bfb);
-            }
-            s.S = take((size_t)B * s.C * L * 4);
+            for (int j = 0; j < g->nk; ++j)
+                for (int m = 0; m < 2; ++m) {
+                    s.r[j][m] = take(bfb);
+                    s.ra[j][m] = take(bfb);
+                }
             s.mrf = take(bfb);
         }
     } else {
@@ -205,7 +207,14 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
                     VO2W_TRY(pack_pair(g->pairs[n][m], W + l1.w_off, W + l1.b_off, W + l2.w_off, W + l2.b_off, ch,
                                        cfg->resblock_kernel_sizes[j], cfg->resblock_dilation_sizes[j][m], g->pair_cg));
                 }
+                for (int m = 0; m < 2; ++m) {
+                    const PackedPair* one[1] = {&g->pairs[n][m]};
+                    VO2W_TRY(make_group(g->iter_group[n][m], one, 1));
+                }
             }
+            const PackedPair* last[3] = {nullptr, nullptr, nullptr};
+            for (int j = 0; j < g->nk; ++j) last[j] = &g->pairs[i * g->nk + j][2];
+            VO2W_TRY(make_group(g->mrf_group[i], last, g->nk));
         }
     }
 #undef VO2W_TRY
@@ -219,8 +228,11 @@ extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
     free_layer(g->conv_pre);
     free_layer(g->conv_post);
     for (int i = 0; i < 4; ++i) free_layer(g->ups[i]);
-    for (int n = 0; n < 12; ++n)
+    for (int i = 0; i < 4; ++i) free_group(g->mrf_group[i]);
+    for (int n = 0; n < 12; ++n) {
+        for (int m = 0; m < 2; ++m) free_group(g->iter_group[n][m]);
         for (int m = 0; m < 3; ++m) free_pair(g->pairs[n][m]);
+    }
     delete g;
     return VO2W_OK;
 }
@@ -243,7 +255,6 @@ namespace {
 int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
     const int B = p.B, T = p.T;
     auto bf = [&](size_t off) { return (__nv_bfloat16*)(ws + off); };
-    auto f32 = [&](size_t off) { return (float*)(ws + off); };
 
     // mel [B,80,T] fp32 -> operand buffer
     VO2W_RUN(pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
@@ -272,27 +283,27 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
         const float next_slope = i + 1 < g->n_stage ? 0.1f : 0.01f;
         for (int j = 0; j < g->nk; ++j) {
             const int n = i * g->nk + j;
-            for (int m = 0; m < 3; ++m) {   // one ResBlock iteration per launch (models.py:97-103)
+            for (int m = 0; m < 2; ++m) {   // one ResBlock iteration per launch (models.py:97-103)
                 PairIO io;
-                io.xa = m == 0 ? bf(s.xa) : bf(s.ra[m - 1]);
-                io.x = m == 0 ? bf(s.x) : bf(s.r[m - 1]);
-                if (m < 2) {
-                    io.mode = PAIR_OUT_STREAM;
-                    io.out_raw = bf(s.r[m]);
-                    io.out_act = bf(s.ra[m]);
-                    io.out_slope = 0.1f;
-                } else {
-                    // xs = sum_j resblocks[j](x); x = xs / num_kernels (models.py:154-160): fp32 running sum,
-                    // the last ResBlock of the stage writes the next layer's operand
-                    io.S = f32(s.S);
-                    io.mode = g->nk == 1 ? PAIR_OUT_SUM_ONLY
-                              : (j == 0 ? PAIR_OUT_SUM_FIRST : (j == g->nk - 1 ? PAIR_OUT_SUM_LAST : PAIR_OUT_SUM_ADD));
-                    io.out_act = bf(s.mrf);
-                    io.out_slope = next_slope;
-                    io.inv_div = 1.0f / (float)g->nk;
-                }
-                VO2W_RUN(pair_launch(g->pairs[n][m], io, B, (int)s.L, st));
+                io.xa[0] = m == 0 ? bf(s.xa) : bf(s.ra[j][0]);
+                io.x[0] = m == 0 ? bf(s.x) : bf(s.r[j][0]);
+                io.out_raw = bf(s.r[j][m]);
+                io.out_act = bf(s.ra[j][m]);
+                io.out_slope = 0.1f;
+                VO2W_RUN(pair_launch(g->iter_group[n][m], io, B, (int)s.L, st));
             }
+        }
+        {   // last iteration of every ResBlock + xs = sum_j resblocks[j](x); x = xs / num_kernels (models.py:154-160)
+            // in ONE launch: the three conv2 accumulate in TMEM, the epilogue adds the three residual streams
+            PairIO io;
+            for (int j = 0; j < g->nk; ++j) {
+                io.xa[j] = bf(s.ra[j][1]);
+                io.x[j] = bf(s.r[j][1]);
+            }
+            io.out_act = bf(s.mrf);
+            io.out_slope = next_slope;
+            io.scale = 1.0f / (float)g->nk;
+            VO2W_RUN(pair_launch(g->mrf_group[i], io, B, (int)s.L, st));
         }
         stage_in = bf(s.mrf);
         L_in = s.L;

@@ -1,73 +1,88 @@
-// Fused ResBlock conv pair on tcgen05 (sm_100a):  r = x + conv2(lrelu(conv1(lrelu(x)) + b1)) + b2
-// (scripts/hifigan/models.py:96-103, one iteration of the ResBlock loop).  See pair_umma.cu and DESIGN.md.
+// Fused ResBlock iterations on tcgen05 (sm_100a).  One launch computes, per 128*NB-row tile,
+//     y = sum over segments s of [ x_s + conv2_s(lrelu(conv1_s(lrelu(x_s)) + b1_s)) + b2_s ]
+// (scripts/hifigan/models.py:96-103 for one segment; with the last iteration of all ResBlocks of a stage as
+// segments it is also the MRF sum xs of models.py:154-160).  See pair_umma.cu and DESIGN.md.
 #pragma once
 #include <vector>
 
 #include "common.cuh"
 
-#define PAIR_THREADS 256          // warp 0 input-tile producer, 1 MMA issuer / peer relay, 2 weight producer,
-                                  // 3 TMEM owner, 4-7 epilogue (TMEM lane quarter = warp & 3)
-#define PAIR_EPI_WARPS 4
+// warp roles: 0 input-tile producer, 1 MMA issuer / peer relay, 2 weight producer, 3 TMEM owner,
+//             4-7 epilogue 1 (conv1 accumulators -> conv2 operand in shared memory),
+//             8-15 epilogue 2 (conv2 accumulators + residuals -> HBM); TMEM lane quarter = warp & 3
+#define PAIR_THREADS 512
+#define PAIR_E1_WARPS 4
+#define PAIR_E2_WARPS 8
 #define PAIR_MAX_SLOTS 4
+#define PAIR_MAX_SEG 3
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
 
-// epilogue of the second convolution
-#define PAIR_OUT_STREAM 0         // out_raw = r (bf16), out_act = lrelu(r, out_slope) (bf16)
-#define PAIR_OUT_SUM_FIRST 1      // S  = r                      (fp32, first ResBlock of the MRF sum)
-#define PAIR_OUT_SUM_ADD 2        // S += r
-#define PAIR_OUT_SUM_ONLY 4       // out_act = lrelu(r * inv_div, out_slope)         (num_kernels == 1)
-#define PAIR_OUT_SUM_LAST 3       // out_act = lrelu((S + r) * inv_div, out_slope)   (x = xs / num_kernels, models.py:154-160)
-
-struct PairP {
+struct PairSegP {
     const __nv_bfloat16* xa;      // conv1 operand = leaky_relu(x, 0.1) as bf16, [B][C/8][Lp][8], zero pad rows
     const __nv_bfloat16* x;       // residual stream x as raw bf16, same layout
-    __nv_bfloat16* out_raw;
-    __nv_bfloat16* out_act;
-    float* S;                     // [B][C/4][L][4]
     const uint8_t* w1;            // packed conv1 weights: [cta rank][item = tap*kbs + kb][KB/8][C/CG][8] bf16
     const uint8_t* w2;
-    const float* bias;            // [2][C]: conv1 bias, conv2 bias
-    int32_t C, L, Lp;
     int32_t k, dil;               // conv1: k taps, dilation dil; conv2: k taps, dilation 1
     int32_t h1, h2;               // halos: dil*(k-1)/2 and (k-1)/2
+    int32_t n_items;              // k * (C / KB)
+    int32_t xa_rows;              // 128*NB + 2*h1
+    uint32_t conv_bytes_rank;     // bytes of one packed conv per CTA rank
+    uint32_t pad_;
+};
+
+struct PairP {
+    PairSegP seg[PAIR_MAX_SEG];
+    int32_t n_seg;
+    __nv_bfloat16* out_raw;       // optional: y * scale as bf16 (the stream for the next iteration)
+    __nv_bfloat16* out_act;       // leaky_relu(bf16(y * scale), out_slope) as bf16 (operand of the next layer)
+    const float* bias;            // [n_seg][C] conv1 biases, then [C] = sum over segments of the conv2 biases
+    int32_t C, L, Lp;
+    int32_t h2max;
     int32_t NB;                   // 128-row accumulator blocks per CTA tile
-    int32_t V;                    // valid output rows per tile = 128*NB - 2*h2
+    int32_t V;                    // valid output rows per tile = 128*NB - 2*h2max
     int32_t tiles_per_utt, n_tiles, iters;
-    int32_t mode;
-    float out_slope, inv_div;
-    int32_t xa_rows, t_rows, xa_bufs;
+    float out_slope, scale;
+    int32_t t_rows, xa_bufs;
     int32_t KB, ksteps, kbs_log2; // input channels per item, K=16 steps per item, log2(C / KB)
-    int32_t n_items, items_per_stage, n_slots;
-    uint32_t item_bytes, stage_bytes, conv_bytes_rank;
+    int32_t items_per_stage, n_slots;
+    uint32_t item_bytes, stage_bytes;
     uint32_t xa_off[2], t_off, ring_off, bias_off;   // byte offsets into dynamic shared memory
     uint32_t smem_bytes;
 };
 
-// Weights of one ResBlock conv pair packed for the kernel (device copies).
+// Weights of one ResBlock iteration (convs1[m], convs2[m]) packed for the kernel.
 struct PackedPair {
     int C = 0, k = 0, dil = 1, cg = 1;
     uint8_t* w1_dev = nullptr;
     uint8_t* w2_dev = nullptr;
-    float* bias_dev = nullptr;    // [2][C]
+    std::vector<float> b1, b2;    // host copies (a launch group concatenates them)
+};
+
+// What one launch runs: 1..3 iterations whose results are summed.
+struct PackedGroup {
+    int n_seg = 0;
+    const PackedPair* seg[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
+    float* bias_dev = nullptr;    // [n_seg][C] + [C]
 };
 
 struct PairIO {
-    const __nv_bfloat16* xa = nullptr;
-    const __nv_bfloat16* x = nullptr;
+    const __nv_bfloat16* xa[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
+    const __nv_bfloat16* x[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
     __nv_bfloat16* out_raw = nullptr;
     __nv_bfloat16* out_act = nullptr;
-    float* S = nullptr;
-    int mode = PAIR_OUT_STREAM;
     float out_slope = 0.1f;
-    float inv_div = 1.0f;
+    float scale = 1.0f;
 };
 
 uint16_t f32_to_bf16_rn(float f);   // pack.cu
-// w1/w2: [C,C,k] fp32 (nn.Conv1d layout), b1/b2: [C].  cg = CTAs per cluster (1 or 2).
+// w1/w2: [C,C,k] fp32 (nn.Conv1d layout), b1/b2: [C].  cg = CTAs per tcgen05 group (1 or 2).
 int pack_pair(PackedPair& P, const float* w1, const float* b1, const float* w2, const float* b2, int C, int k, int dil,
               int cg);
 void free_pair(PackedPair& P);
+int make_group(PackedGroup& G, const PackedPair* const* pairs, int n_seg);
+void free_group(PackedGroup& G);
 // host-side layout of one conv ([rank][item][chunk][n_local][8] bf16 bits); exposed for the CPU tests
 void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, int C, int k, int cg);
-int pair_plan(PairP& p, int C, int k, int dil, int cg, int B, int L, int n_sms);
-int pair_launch(const PackedPair& P, const PairIO& io, int B, int L, cudaStream_t st);
+// fills the geometry of a launch (no pointers); returns the grid size or a negative error
+int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms);
+int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st);
