@@ -47,13 +47,13 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
     return r;
 }
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
         : "r"(bar), "r"(parity)
@@ -167,54 +167,90 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     return t;
 }
 
-// One convolution = n_items weight items (tap, 64-channel block), each applied to all NB row blocks.
+// MMA with both shared-memory descriptors given as their low words (start address and LBO; the high word
+// -- SBO = 128 B, descriptor version 1 -- is the same constant for every operand of this kernel).
+template <int CG>
+__device__ __forceinline__ void mma_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t acc) {
+    if (CG == 1)
+        asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+                     "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_lo), "r"(b_lo),
+                     "r"(idesc), "r"(acc), "r"(0x4008u) : "memory");
+    else
+        asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+                     "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_lo), "r"(b_lo),
+                     "r"(idesc), "r"(acc), "r"(0x4008u) : "memory");
+}
+
+// One convolution = the bias item followed by the (tap, 64-channel block) weight items, each applied to all
+// NB row blocks.
 // second: reads the conv2 operand buffer (dilation 1; block c > 0 starts at row c*128 - 2*h2max).
 // keep:   accumulate on top of what the accumulators hold (conv2 of segments after the first).
-template <int CG>
+// The whole warp walks the (warp-uniform) loops so that addresses stay in uniform registers; one elected
+// lane issues.  All descriptor arithmetic is in 16-byte units on the low descriptor word.
+template <int CG, int NB, int KS>
 __device__ __forceinline__ void issue_conv(const PairP& p, uint32_t bar0, uint32_t a_addr, uint32_t a_rows, int n_items,
                                            int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
-                                           uint32_t idesc, uint32_t& wit) {
+                                           uint32_t idesc, uint32_t ones_lo, uint32_t& wit, long long& w_wait) {
     const uint32_t n_loc = (uint32_t)p.C / CG;
-    const uint32_t b_lbo = n_loc * 16u, a_lbo = a_rows * 16u;
-    const uint64_t a_hi = ((uint64_t)(a_lbo >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | ((uint64_t)1 << 46);
-    const uint64_t b_hi = ((uint64_t)(b_lbo >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | ((uint64_t)1 << 46);
+    const uint32_t a_base = ((a_addr >> 4) & 0x3FFFu) | (a_rows << 16);      // LBO = a_rows * 16 B
+    const uint32_t b_lbo_field = n_loc << 16;                                 // LBO = n_loc * 16 B
     const int kbs_mask = (1 << p.kbs_log2) - 1;
-    const uint32_t chunks_per_kb = (uint32_t)p.KB >> 3;
-    const int blk_back = second ? 2 * p.h2max : 0;
+    const uint32_t kb_rows = ((uint32_t)p.KB >> 3) * a_rows;                  // 16-byte units per 64-channel block
+    const uint32_t blk_back = second ? 2u * (uint32_t)p.h2max : 0u;
+    const uint32_t item_units = p.item_bytes >> 4;
     int item = 0;
     while (item < n_items) {
         const uint32_t slot = wit % (uint32_t)p.n_slots, par = (wit / (uint32_t)p.n_slots) & 1u;
+        const long long tw = clock64();
         mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
         if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL_PEER + slot), par);
+        w_wait += clock64() - tw;
+        __syncwarp();
         tc_fence_after();
         const int cnt = min(p.items_per_stage, n_items - item);
-        if (elect_one()) {
-            const uint32_t stage = ring_addr + slot * p.stage_bytes;
-            for (int i = 0; i < cnt; ++i) {
-                const int idx = item + i;
-                const int tap = idx >> p.kbs_log2, kb = idx & kbs_mask;
-                const uint32_t b_item = stage + (uint32_t)i * p.item_bytes;
-                for (int blk = 0; blk < p.NB; ++blk) {
-                    const int row0 = blk * 128 - (blk > 0 ? blk_back : 0) + tap * dil;
-                    const uint32_t a_blk = a_addr + ((uint32_t)kb * chunks_per_kb * a_rows + (uint32_t)row0) * 16u;
-                    const uint32_t d = d_tmem + (uint32_t)(blk * p.C);
-                    for (int s = 0; s < p.ksteps; ++s) {
-                        const uint64_t ad = a_hi | (uint64_t)(((a_blk + (uint32_t)s * 2u * a_lbo) >> 4) & 0x3FFFu);
-                        const uint64_t bd = b_hi | (uint64_t)(((b_item + (uint32_t)s * 2u * b_lbo) >> 4) & 0x3FFFu);
-                        mma_bf16<CG>(d, ad, bd, idesc, (keep || (idx | s) != 0) ? 1u : 0u);
-                    }
+        const uint32_t stage_lo = (((ring_addr + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
+        for (int i = 0; i < cnt; ++i) {
+            const int idx = item + i;
+            const uint32_t b_lo = stage_lo + (uint32_t)i * item_units;
+            if (idx == 0) {
+                // item 0 is the bias: D = ones[128 x 16] . (b_hi, b_lo, 0, ...)^T initialises the accumulators
+                if (elect_one()) {
+#pragma unroll
+                    for (int blk = 0; blk < NB; ++blk)
+                        mma_lo<CG>(d_tmem + (uint32_t)(blk * p.C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
+                }
+                __syncwarp();
+                continue;
+            }
+            const uint32_t tap = (uint32_t)((idx - 1) >> p.kbs_log2), kb = (uint32_t)((idx - 1) & kbs_mask);
+            const uint32_t a_lo = a_base + kb * kb_rows + tap * (uint32_t)dil;
+            if (elect_one()) {
+#pragma unroll
+                for (int blk = 0; blk < NB; ++blk) {
+                    const uint32_t a_blk = a_lo + (uint32_t)(blk * 128) - (blk > 0 ? blk_back : 0u);
+#pragma unroll
+                    for (int s = 0; s < KS; ++s)
+                        mma_lo<CG>(d_tmem + (uint32_t)(blk * p.C), a_blk + (uint32_t)s * 2u * a_rows,
+                                   b_lo + (uint32_t)s * 2u * n_loc, idesc, 1u);
                 }
             }
-            mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
+            __syncwarp();
         }
+        if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
         __syncwarp();
         item += cnt;
         ++wit;
     }
 }
 
-template <int CG>
+template <int CG, int C>
 __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid_constant__ PairP p) {
+    constexpr int NB = C >= 256 ? 1 : (C >= 64 ? 2 : 4);     // 128-row accumulator blocks per tile (2*NB*C <= 512 TMEM columns)
+    constexpr int KS = C < 64 ? 2 : 4;                       // K=16 steps per weight item (64 input channels, 32 for C=32)
+    constexpr int GROUPS = C / 32;                           // 32 accumulator columns per tcgen05.ld
+    constexpr int CHUNKS = C / 8;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[BAR_COUNT];
     __shared__ uint32_t tmem_base_s;
@@ -223,25 +259,28 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
     const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
     const uint32_t sm0 = smem_u32(smem);
     const uint32_t bar0 = smem_u32(bars);
-    const int C = p.C, NB = p.NB, n_seg = p.n_seg;
+    const int n_seg = p.n_seg;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < BAR_COUNT; ++i)
             mbar_init(bar0 + 8u * i, i == BAR_T_FULL ? CG * PAIR_E1_WARPS : (i == BAR_D2_EMPTY ? CG * PAIR_E2_WARPS : 1));
         fence_mbar_init();
     }
-    if (warp == 3) tmem_alloc_cg<CG>(smem_u32(&tmem_base_s), 512u);
-    for (int i = threadIdx.x; i < (n_seg + 1) * C; i += PAIR_THREADS) ((float*)(smem + p.bias_off))[i] = __ldg(p.bias + i);
+    if (warp == PAIR_WARP_TMEM) tmem_alloc_cg<CG>(smem_u32(&tmem_base_s), 512u);
+    // A operand of the bias MMA: 128 rows x K=16 with ones in the first two K columns (bias = hi + lo in bf16)
+    if (threadIdx.x < 256)
+        st_shared_v4(sm0 + p.ones_off + threadIdx.x * 16u, make_uint4(threadIdx.x < 128 ? 0x3F803F80u : 0u, 0u, 0u, 0u));
+    fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     if (CG == 2) cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
 
-    if (warp == 0) {
+    if (warp == PAIR_WARP_XA) {
         // ================= input tile producer =================
         if (lane == 0) {
-            const int chunks = C >> 3;
+            constexpr int chunks = CHUNKS;
             int n = 0;                                   // running (tile, segment) counter -> buffer and phase
             for (int it = 0; it < p.iters; ++it) {
                 const TileCoord t = tile_of(p, it);
@@ -266,7 +305,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
             }
         }
-    } else if (warp == 2) {
+    } else if (warp == PAIR_WARP_W) {
         // ================= weight producer =================
         if (lane == 0) {
             uint32_t wit = 0;
@@ -288,38 +327,53 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == PAIR_WARP_MMA) {
         if (rank == 0) {
             // ================= MMA issuer (whole warp loops, one elected lane issues) =================
             const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
+            const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
             const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(NB * C);
             uint32_t wit = 0;
             int n = 0;
+            long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0;
+            const long long c_start = clock64();
             for (int it = 0; it < p.iters; ++it) {
                 for (int s = 0; s < n_seg; ++s, ++n) {
                     const PairSegP& sg = p.seg[s];
                     const int buf = n % p.xa_bufs, use = n / p.xa_bufs;
+                    long long c0 = clock64();
                     mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
                     if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
+                    c_xa += clock64() - c0;
                     tc_fence_after();
-                    issue_conv<CG>(p, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false, d1,
-                                   sm0 + p.ring_off, idesc, wit);
+                    issue_conv<CG, NB, KS>(p, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false, d1,
+                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w);
                     if (elect_one()) {
                         mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));   // input tile reusable
                         mma_commit<CG>(bar0 + 8u * BAR_D1_FULL);            // e1 may start
                     }
                     __syncwarp();
                     // conv2 operand written by all e1 warps of the pair; D2 drained by the previous tile's e2
+                    c0 = clock64();
                     mbar_wait_cluster(bar0 + 8u * BAR_T_FULL, (uint32_t)(n & 1));
+                    c_t += clock64() - c0;
+                    c0 = clock64();
                     if (s == 0 && it > 0) mbar_wait_cluster(bar0 + 8u * BAR_D2_EMPTY, (uint32_t)((it - 1) & 1));
+                    c_d2 += clock64() - c0;
                     tc_fence_after();
-                    issue_conv<CG>(p, bar0, sm0 + p.t_off, (uint32_t)p.t_rows, sg.n_items, 1, true, s > 0, d2,
-                                   sm0 + p.ring_off, idesc, wit);
+                    issue_conv<CG, NB, KS>(p, bar0, sm0 + p.t_off, (uint32_t)p.t_rows, sg.n_items, 1, true, s > 0, d2,
+                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w);
                     if (s == n_seg - 1) {
                         if (elect_one()) mma_commit<CG>(bar0 + 8u * BAR_D2_FULL);
                         __syncwarp();
                     }
                 }
+            }
+            if (p.prof && lane == 0) {
+                unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
+                o[0] = (unsigned long long)(clock64() - c_start);
+                o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
+                o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2;
             }
         } else if (lane == 0) {
             // ================= peer relay: forward "landed" events to the leader's barriers =================
@@ -340,45 +394,57 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             }
         }
     }
-    else if (warp >= 4 && warp < 4 + PAIR_E1_WARPS) {
+    else if (warp >= PAIR_E1_WARP0 && warp < PAIR_E1_WARP0 + PAIR_E1_WARPS) {
         // ================= e1: conv1 accumulators -> bf16 conv2 operand in shared memory =================
+        // On the critical path of every segment (conv2 cannot start before it ends): fully unrolled, two TMEM
+        // loads in flight per warp.
+        constexpr int UNITS = GROUPS * NB;               // (32-column group, row block) units per warp, two in flight
         const int q4 = warp & 3;                         // TMEM lane quarter this warp may read
         const int q = q4 * 32 + lane;                    // row inside a 128-row block
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t t_full_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_T_FULL, 0) : 0u;
-        const int groups = C >> 5;                       // 32 accumulator columns per tcgen05.ld
         const __nv_bfloat162 slope2 = __floats2bfloat162_rn(0.1f, 0.1f);
+        const uint32_t t_row0 = sm0 + p.t_off + (uint32_t)q * 16u;
+        // convert 32 accumulator columns of one row block: bf16, leaky-relu, 4 x 16-byte stores
+        auto convert = [&](const uint32_t (&r)[32], int g, int blk, bool inside) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+                uint4 o;
+                o.x = pack_bf16x2(__uint_as_float(r[h * 8 + 0]), __uint_as_float(r[h * 8 + 1]));
+                o.y = pack_bf16x2(__uint_as_float(r[h * 8 + 2]), __uint_as_float(r[h * 8 + 3]));
+                o.z = pack_bf16x2(__uint_as_float(r[h * 8 + 4]), __uint_as_float(r[h * 8 + 5]));
+                o.w = pack_bf16x2(__uint_as_float(r[h * 8 + 6]), __uint_as_float(r[h * 8 + 7]));
+                o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
+                o.z = lrelu_bf16x2(o.z, slope2); o.w = lrelu_bf16x2(o.w, slope2);
+                if (!inside) o = make_uint4(0u, 0u, 0u, 0u);
+                st_shared_v4(t_row0 + (uint32_t)(((g * 4 + h) * NB * 128 + blk * 128) * 16), o);
+            }
+        };
         int n = 0;
+        long long c_wait = 0, c_work = 0, c_fence = 0, c_ld = 0;
         for (int it = 0; it < p.iters; ++it) {
             const TileCoord t = tile_of(p, it);
             for (int s = 0; s < n_seg; ++s, ++n) {
-                const float* sb1 = (const float*)(smem + p.bias_off) + s * C;
-                const int t0 = t.l0 - p.seg[s].h2;       // sample index of operand row 0
+                const int t0 = t.l0 - p.seg[s].h2 + q;   // sample index of this thread's operand row in block 0
+                const long long c0 = clock64();
                 mbar_wait(bar0 + 8u * BAR_D1_FULL, (uint32_t)(n & 1));
+                const long long c1 = clock64();
+                c_wait += c1 - c0;
                 tc_fence_after();
-                for (int blk = 0; blk < NB; ++blk) {
-                    const int grow = t0 + blk * 128 + q;
-                    const bool inside = grow >= 0 && grow < p.L;           // conv2 zero-pads outside the utterance
-                    const uint32_t t_row = sm0 + p.t_off + (uint32_t)(blk * 128 + q) * 16u;
-                    for (int g = 0; g < groups; ++g) {
-                        uint32_t r[32];
-                        tmem_ld32(t_lane + (uint32_t)(blk * C + g * 32), r);
-                        tmem_ld_wait();
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) {
-                            const float4 ba = *(const float4*)(sb1 + g * 32 + h * 8), bb = *(const float4*)(sb1 + g * 32 + h * 8 + 4);
-                            uint4 o;
-                            o.x = pack_bf16x2(__uint_as_float(r[h * 8 + 0]) + ba.x, __uint_as_float(r[h * 8 + 1]) + ba.y);
-                            o.y = pack_bf16x2(__uint_as_float(r[h * 8 + 2]) + ba.z, __uint_as_float(r[h * 8 + 3]) + ba.w);
-                            o.z = pack_bf16x2(__uint_as_float(r[h * 8 + 4]) + bb.x, __uint_as_float(r[h * 8 + 5]) + bb.y);
-                            o.w = pack_bf16x2(__uint_as_float(r[h * 8 + 6]) + bb.z, __uint_as_float(r[h * 8 + 7]) + bb.w);
-                            o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
-                            o.z = lrelu_bf16x2(o.z, slope2); o.w = lrelu_bf16x2(o.w, slope2);
-                            if (!inside) o = make_uint4(0u, 0u, 0u, 0u);
-                            st_shared_v4(t_row + (uint32_t)((g * 4 + h) * p.t_rows) * 16u, o);
-                        }
-                    }
+                for (int u = 0; u < UNITS; u += 2) {             // g-major unit order; both loads precede the wait
+                    const int g0 = u / NB, b0 = u % NB, g1 = (u + 1) / NB, b1 = (u + 1) % NB;
+                    uint32_t ra[32], rb[32];
+                    const long long cl0 = clock64();
+                    tmem_ld32(t_lane + (uint32_t)(b0 * C + g0 * 32), ra);
+                    tmem_ld32(t_lane + (uint32_t)(b1 * C + g1 * 32), rb);
+                    tmem_ld_wait();
+                    c_ld += clock64() - cl0;
+                    const int r0 = t0 + b0 * 128, r1 = t0 + b1 * 128;      // conv2 zero-pads outside the utterance
+                    convert(ra, g0, b0, r0 >= 0 && r0 < p.L);
+                    convert(rb, g1, b1, r1 >= 0 && r1 < p.L);
                 }
+                const long long c2 = clock64();
                 fence_proxy_async();                     // generic-proxy stores -> visible to the tensor core (async proxy)
                 tc_fence_before();
                 __syncwarp();
@@ -386,33 +452,47 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     if (CG == 2) mbar_arrive_remote(t_full_addr);
                     else mbar_arrive(bar0 + 8u * BAR_T_FULL);
                 }
+                c_work += clock64() - c1;
+                c_fence += clock64() - c2;
             }
         }
-    } else if (warp >= 4 + PAIR_E1_WARPS) {
-        // ================= e2: conv2 accumulators + biases + residuals -> global =================
+        if (p.prof && warp == PAIR_E1_WARP0 && lane == 0) {
+            p.prof[(size_t)blockIdx.x * 16 + 5] = (unsigned long long)c_wait;
+            p.prof[(size_t)blockIdx.x * 16 + 6] = (unsigned long long)c_work;
+            p.prof[(size_t)blockIdx.x * 16 + 9] = (unsigned long long)c_ld;
+        }
+    } else if (warp < PAIR_E2_WARPS) {
+        // ================= e2: conv2 accumulators + residuals -> global =================
+        // Runs behind the MMAs of the next tile.  Two warps per lane quarter split the (block, 32-column group)
+        // items; residual rows (prefetched into L2 by the producer) are fetched before the accumulators are
+        // ready: all items at once for a single segment, item by item for the MRF launch.
+        constexpr int ITEMS = NB * GROUPS / 2;           // per warp
         const int q4 = warp & 3;
         const int q = q4 * 32 + lane;
-        const int half = (warp - 4 - PAIR_E1_WARPS) >> 2;        // two warps per lane quarter split the (block, group) items
+        const int half = warp >> 2;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t d2_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D2_EMPTY, 0) : 0u;
-        const float* sb2 = (const float*)(smem + p.bias_off) + n_seg * C;
-        const int groups = C >> 5, chunks = C >> 3;
-        const int n_work = NB * groups;
         const size_t e_step = (size_t)p.Lp * 8;
         const __nv_bfloat162 slope2 = __floats2bfloat162_rn(p.out_slope, p.out_slope);
+        const bool single = n_seg == 1;
+        const int back = 2 * p.h2max;
+        long long c_wait = 0, c_work = 0;
         for (int it = 0; it < p.iters; ++it) {
             const TileCoord t = tile_of(p, it);
-            uint4 R[PAIR_MAX_SEG][4];
-            auto row_of = [&](int i, int& blk, int& g, int& orow) {
-                blk = i / groups;
-                g = i - blk * groups;
-                orow = t.l0 + (blk == 0 ? 0 : blk * 128 - 2 * p.h2max) + q;
-                return t.live && orow < p.L && (blk > 0 || q < 128 - 2 * p.h2max);
+            const size_t e_tile = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8;   // chunk 0, block 0 row of this thread
+            uint4 R[4][4];                               // single: [item][chunk]; MRF: [segment][chunk] of the current item
+            auto item_geom = [&](int j, int& blk, int& g, int& rel, bool& ok) {
+                const int i = half + 2 * j;
+                blk = i / GROUPS;
+                g = i % GROUPS;
+                rel = blk == 0 ? 0 : blk * 128 - back;
+                ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back);
             };
-            auto load_res = [&](int i) {
-                int blk, g, orow;
-                if (!row_of(i, blk, g, orow)) return;
-                const size_t e = ((size_t)t.b * chunks * p.Lp + VO2W_PAD_ROWS + orow) * 8 + (size_t)(g * 4) * e_step;
+            auto load_item = [&](int j) {                // MRF launch: all segments of item j
+                int blk, g, rel; bool ok;
+                item_geom(j, blk, g, rel, ok);
+                if (!ok) return;
+                const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
 #pragma unroll
                 for (int s = 0; s < PAIR_MAX_SEG; ++s)
                     if (s < n_seg) {
@@ -420,45 +500,65 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                         for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].x + e + (size_t)h * e_step));
                     }
             };
-            if (half < n_work) load_res(half);           // residuals do not depend on the accumulators: fetch first
+            if (single) {
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    int blk, g, rel; bool ok;
+                    item_geom(j, blk, g, rel, ok);
+                    if (ok) {
+                        const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].x + e + (size_t)h * e_step));
+                    }
+                }
+            } else {
+                load_item(0);
+            }
+            const long long c0 = clock64();
             mbar_wait(bar0 + 8u * BAR_D2_FULL, (uint32_t)(it & 1));
+            const long long c1 = clock64();
+            c_wait += c1 - c0;
             tc_fence_after();
-            for (int i = half; i < n_work; i += 2) {
-                int blk, g, orow;
-                const bool ok = row_of(i, blk, g, orow);
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) {
+                int blk, g, rel; bool ok;
+                item_geom(j, blk, g, rel, ok);
                 uint32_t r[32];
                 tmem_ld32(t_lane + (uint32_t)((NB + blk) * C + g * 32), r);
                 tmem_ld_wait();
                 float v[32];
 #pragma unroll
-                for (int c4 = 0; c4 < 8; ++c4) {
-                    const float4 b = *(const float4*)(sb2 + g * 32 + c4 * 4);
-                    v[c4 * 4 + 0] = __uint_as_float(r[c4 * 4 + 0]) + b.x; v[c4 * 4 + 1] = __uint_as_float(r[c4 * 4 + 1]) + b.y;
-                    v[c4 * 4 + 2] = __uint_as_float(r[c4 * 4 + 2]) + b.z; v[c4 * 4 + 3] = __uint_as_float(r[c4 * 4 + 3]) + b.w;
-                }
-                if (ok) {
+                for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]);
+                auto add_res = [&](const uint4 (&x)[4]) {
 #pragma unroll
-                    for (int s = 0; s < PAIR_MAX_SEG; ++s)
-                        if (s < n_seg) {
-#pragma unroll
-                            for (int h = 0; h < 4; ++h) {
-                                const float2 x0 = unpack_bf16x2(R[s][h].x), x1 = unpack_bf16x2(R[s][h].y);
-                                const float2 x2 = unpack_bf16x2(R[s][h].z), x3 = unpack_bf16x2(R[s][h].w);
-                                v[h * 8 + 0] += x0.x; v[h * 8 + 1] += x0.y; v[h * 8 + 2] += x1.x; v[h * 8 + 3] += x1.y;
-                                v[h * 8 + 4] += x2.x; v[h * 8 + 5] += x2.y; v[h * 8 + 6] += x3.x; v[h * 8 + 7] += x3.y;
-                            }
-                        }
-                }
-                if (i + 2 < n_work) load_res(i + 2);     // next item's residuals fly while this one is stored
+                    for (int h = 0; h < 4; ++h) {
+                        const float2 x0 = unpack_bf16x2(x[h].x), x1 = unpack_bf16x2(x[h].y);
+                        const float2 x2 = unpack_bf16x2(x[h].z), x3 = unpack_bf16x2(x[h].w);
+                        v[h * 8 + 0] += x0.x; v[h * 8 + 1] += x0.y; v[h * 8 + 2] += x1.x; v[h * 8 + 3] += x1.y;
+                        v[h * 8 + 4] += x2.x; v[h * 8 + 5] += x2.y; v[h * 8 + 6] += x3.x; v[h * 8 + 7] += x3.y;
+                    }
+                };
                 if (ok) {
-                    const size_t e = ((size_t)t.b * chunks * p.Lp + VO2W_PAD_ROWS + orow) * 8 + (size_t)(g * 4) * e_step;
+                    if (single) {
+                        add_res(R[j]);
+                    } else {
+#pragma unroll
+                        for (int s = 0; s < PAIR_MAX_SEG; ++s)
+                            if (s < n_seg) add_res(R[s]);
+                    }
+                }
+                if (!single && j + 1 < ITEMS) load_item(j + 1);  // next item's residuals fly while this one is stored
+                if (ok) {
+                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+                    if (p.scale != 1.0f) {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) v[c] *= p.scale;
+                    }
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
                         uint4 o;
-                        o.x = pack_bf16x2(v[h * 8 + 0] * p.scale, v[h * 8 + 1] * p.scale);
-                        o.y = pack_bf16x2(v[h * 8 + 2] * p.scale, v[h * 8 + 3] * p.scale);
-                        o.z = pack_bf16x2(v[h * 8 + 4] * p.scale, v[h * 8 + 5] * p.scale);
-                        o.w = pack_bf16x2(v[h * 8 + 6] * p.scale, v[h * 8 + 7] * p.scale);
+                        o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
+                        o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
                         if (p.out_raw) *(uint4*)(p.out_raw + e + (size_t)h * e_step) = o;
                         // the activation is taken of the ROUNDED stream value (what a reader of the stream would compute)
                         o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
@@ -473,13 +573,18 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 if (CG == 2) mbar_arrive_remote(d2_empty_addr);
                 else mbar_arrive(bar0 + 8u * BAR_D2_EMPTY);
             }
+            c_work += clock64() - c1;
+        }
+        if (p.prof && warp == 0 && lane == 0) {
+            p.prof[(size_t)blockIdx.x * 16 + 7] = (unsigned long long)c_wait;
+            p.prof[(size_t)blockIdx.x * 16 + 8] = (unsigned long long)c_work;
         }
     }
 
     tc_fence_before();
     __syncthreads();
     if (CG == 2) cluster_sync_all();
-    if (warp == 3) tmem_dealloc_cg<CG>(tmem_base, 512u);
+    if (warp == PAIR_WARP_TMEM) tmem_dealloc_cg<CG>(tmem_base, 512u);
 }
 
 }  // namespace
@@ -487,11 +592,23 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
 // ---------------------------------------------------------------------------------------------------
 // host side: weight packing, tile plan, launch
 // ---------------------------------------------------------------------------------------------------
-void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, int C, int k, int cg) {
+void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, const float* bias, int C, int k, int cg) {
     const int KB = C < 64 ? C : 64, kbs = C / KB, n_loc = C / cg;
-    out.assign((size_t)C * C * k, 0);
+    const size_t item = (size_t)n_loc * KB;                      // elements of one item of one rank
+    out.assign((size_t)cg * (k * kbs + 1) * item, 0);
     size_t o = 0;
-    for (int rank = 0; rank < cg; ++rank)
+    for (int rank = 0; rank < cg; ++rank) {
+        // item 0: the bias as a K=16 operand, columns 0/1 = bf16 hi/lo parts (the A operand has ones there)
+        for (int n = 0; n < n_loc; ++n) {
+            const float b = bias[rank * n_loc + n];
+            const uint16_t hi = f32_to_bf16_rn(b);
+            uint32_t hb = (uint32_t)hi << 16;
+            float hf;
+            memcpy(&hf, &hb, 4);
+            out[o + (size_t)n * 8 + 0] = hi;
+            out[o + (size_t)n * 8 + 1] = f32_to_bf16_rn(b - hf);
+        }
+        o += item;
         for (int tap = 0; tap < k; ++tap)
             for (int kb = 0; kb < kbs; ++kb)
                 for (int chunk = 0; chunk < KB / 8; ++chunk)
@@ -500,25 +617,23 @@ void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, int C, int 
                             const int co = rank * n_loc + n, ci = kb * KB + chunk * 8 + e;
                             out[o++] = f32_to_bf16_rn(w[((size_t)co * C + ci) * k + tap]);
                         }
+    }
 }
 
 int pack_pair(PackedPair& P, const float* w1, const float* b1, const float* w2, const float* b2, int C, int k, int dil,
               int cg) {
-    VO2W_REQUIRE(C % 32 == 0 && C >= 32 && C <= 256, "pack_pair: channels %d unsupported (need a multiple of 32 in 32..256)", C);
+    VO2W_REQUIRE(C == 32 || C == 64 || C == 128 || C == 256, "pack_pair: channels %d unsupported (32, 64, 128 or 256)", C);
     VO2W_REQUIRE((k & 1) && k >= 1 && k <= 11, "pack_pair: kernel size %d unsupported", k);
     VO2W_REQUIRE(cg == 1 || cg == 2, "pack_pair: cluster size %d", cg);
     VO2W_REQUIRE((dil + 1) * (k - 1) / 2 <= VO2W_PAD_ROWS - 2, "pack_pair: halo exceeds the pad rows (k=%d dil=%d)", k, dil);
     P.C = C; P.k = k; P.dil = dil; P.cg = cg;
-    P.b1.assign(b1, b1 + C);
-    P.b2.assign(b2, b2 + C);
     std::vector<uint16_t> h;
-    const size_t bytes = (size_t)C * C * k * 2;
-    pack_pair_conv_host(h, w1, C, k, cg);
-    VO2W_CUDA_OK(cudaMalloc(&P.w1_dev, bytes));
-    VO2W_CUDA_OK(cudaMemcpy(P.w1_dev, h.data(), bytes, cudaMemcpyHostToDevice));
-    pack_pair_conv_host(h, w2, C, k, cg);
-    VO2W_CUDA_OK(cudaMalloc(&P.w2_dev, bytes));
-    VO2W_CUDA_OK(cudaMemcpy(P.w2_dev, h.data(), bytes, cudaMemcpyHostToDevice));
+    pack_pair_conv_host(h, w1, b1, C, k, cg);
+    VO2W_CUDA_OK(cudaMalloc(&P.w1_dev, h.size() * 2));
+    VO2W_CUDA_OK(cudaMemcpy(P.w1_dev, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+    pack_pair_conv_host(h, w2, b2, C, k, cg);
+    VO2W_CUDA_OK(cudaMalloc(&P.w2_dev, h.size() * 2));
+    VO2W_CUDA_OK(cudaMemcpy(P.w2_dev, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
     return VO2W_OK;
 }
 
@@ -530,27 +645,15 @@ void free_pair(PackedPair& P) {
 
 int make_group(PackedGroup& G, const PackedPair* const* pairs, int n_seg) {
     VO2W_REQUIRE(n_seg >= 1 && n_seg <= PAIR_MAX_SEG, "make_group: %d segments", n_seg);
-    const int C = pairs[0]->C;
-    std::vector<float> b((size_t)(n_seg + 1) * C, 0.f);
     for (int s = 0; s < n_seg; ++s) {
-        VO2W_REQUIRE(pairs[s]->C == C && pairs[s]->cg == pairs[0]->cg, "make_group: segments must share channels and cluster size");
+        VO2W_REQUIRE(pairs[s]->C == pairs[0]->C && pairs[s]->cg == pairs[0]->cg, "make_group: segments must share channels and cluster size");
         G.seg[s] = pairs[s];
-        for (int c = 0; c < C; ++c) {
-            b[(size_t)s * C + c] = pairs[s]->b1[c];
-            b[(size_t)n_seg * C + c] += pairs[s]->b2[c];
-        }
     }
     G.n_seg = n_seg;
-    VO2W_CUDA_OK(cudaMalloc(&G.bias_dev, b.size() * 4));
-    VO2W_CUDA_OK(cudaMemcpy(G.bias_dev, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
     return VO2W_OK;
 }
 
-void free_group(PackedGroup& G) {
-    if (G.bias_dev) cudaFree(G.bias_dev);
-    G.bias_dev = nullptr;
-    G.n_seg = 0;
-}
+void free_group(PackedGroup& G) { G.n_seg = 0; }
 
 int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms) {
     memset(&p, 0, sizeof(p));
@@ -568,9 +671,9 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
         sg.k = ks[s]; sg.dil = dils[s];
         sg.h1 = dils[s] * (ks[s] - 1) / 2;
         sg.h2 = (ks[s] - 1) / 2;
-        sg.n_items = ks[s] * kbs;
+        sg.n_items = ks[s] * kbs + 1;                 // bias item + (tap, channel block) items
         sg.xa_rows = 128 * p.NB + 2 * sg.h1;
-        sg.conv_bytes_rank = (uint32_t)((size_t)C * C * ks[s] * 2 / cg);
+
         if (sg.h1 > h1max) h1max = sg.h1;
         if (sg.h2 > p.h2max) p.h2max = sg.h2;
         if (ks[s] > kmax) kmax = ks[s];
@@ -579,22 +682,23 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     p.tiles_per_utt = vo2w_ceil_div(L, p.V);
     p.n_tiles = B * p.tiles_per_utt;
     p.item_bytes = (uint32_t)(C / cg) * p.KB * 2;
+    for (int s = 0; s < n_seg; ++s) p.seg[s].conv_bytes_rank = (uint32_t)p.seg[s].n_items * p.item_bytes;
     p.items_per_stage = (int)(16384u / p.item_bytes);
     if (p.items_per_stage < 1) p.items_per_stage = 1;
-    if (p.items_per_stage > kmax * kbs) p.items_per_stage = kmax * kbs;
+    if (p.items_per_stage > kmax * kbs + 1) p.items_per_stage = kmax * kbs + 1;
     p.stage_bytes = (uint32_t)p.items_per_stage * p.item_bytes;
     p.n_slots = p.stage_bytes > 16384u ? 2 : PAIR_MAX_SLOTS;
     p.t_rows = 128 * p.NB;
     const uint32_t xa_bytes = (uint32_t)(128 * p.NB + 2 * h1max) * C * 2, t_bytes = (uint32_t)p.t_rows * C * 2;
-    const uint32_t bias_bytes = (uint32_t)(n_seg + 1) * C * 4u;
-    const uint32_t fixed = t_bytes + (uint32_t)p.n_slots * p.stage_bytes + bias_bytes;
+    const uint32_t ones_bytes = 2u * 128u * 16u;
+    const uint32_t fixed = t_bytes + (uint32_t)p.n_slots * p.stage_bytes + ones_bytes;
     p.xa_bufs = (fixed + 2 * xa_bytes <= PAIR_SMEM_LIMIT) ? 2 : 1;
     uint32_t off = 0;
     for (int i = 0; i < p.xa_bufs; ++i) { p.xa_off[i] = off; off += xa_bytes; }
     if (p.xa_bufs == 1) p.xa_off[1] = p.xa_off[0];
     p.t_off = off; off += t_bytes;
     p.ring_off = off; off += (uint32_t)p.n_slots * p.stage_bytes;
-    p.bias_off = off; off += bias_bytes;
+    p.ones_off = off; off += ones_bytes;
     p.smem_bytes = off;
     VO2W_REQUIRE(off <= PAIR_SMEM_LIMIT, "pair_plan: %u bytes of shared memory (C=%d)", off, C);
     int grid = n_sms / cg * cg;
@@ -604,6 +708,12 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     return grid;
 }
 
+typedef void (*pair_kernel_t)(const PairP);
+static pair_kernel_t pair_kernel_for(int cg, int C) {
+    if (cg == 2) return C == 256 ? pair_umma_kernel<2, 256> : (C == 128 ? pair_umma_kernel<2, 128> : (C == 64 ? pair_umma_kernel<2, 64> : pair_umma_kernel<2, 32>));
+    return C == 256 ? pair_umma_kernel<1, 256> : (C == 128 ? pair_umma_kernel<1, 128> : (C == 64 ? pair_umma_kernel<1, 64> : pair_umma_kernel<1, 32>));
+}
+
 int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st) {
     static int n_sms = 0;
     static bool attr_set = false;
@@ -611,11 +721,12 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
         int dev = 0;
         VO2W_CUDA_OK(cudaGetDevice(&dev));
         VO2W_CUDA_OK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
-        VO2W_CUDA_OK(cudaFuncSetAttribute(pair_umma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
-        VO2W_CUDA_OK(cudaFuncSetAttribute(pair_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
+        for (int cgi = 1; cgi <= 2; ++cgi)
+            for (int c = 32; c <= 256; c *= 2)
+                VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(cgi, c), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
         attr_set = true;
     }
-    VO2W_REQUIRE(G.n_seg >= 1 && G.bias_dev && io.out_act, "pair_launch: incomplete group or missing output");
+    VO2W_REQUIRE(G.n_seg >= 1 && io.out_act, "pair_launch: incomplete group or missing output");
     const int cg = G.seg[0]->cg;
     int ks[PAIR_MAX_SEG], dils[PAIR_MAX_SEG];
     for (int s = 0; s < G.n_seg; ++s) { ks[s] = G.seg[s]->k; dils[s] = G.seg[s]->dil; }
@@ -627,7 +738,7 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
         p.seg[s].xa = io.xa[s]; p.seg[s].x = io.x[s];
         p.seg[s].w1 = G.seg[s]->w1_dev; p.seg[s].w2 = G.seg[s]->w2_dev;
     }
-    p.out_raw = io.out_raw; p.out_act = io.out_act; p.bias = G.bias_dev;
+    p.out_raw = io.out_raw; p.out_act = io.out_act;
     p.out_slope = io.out_slope; p.scale = io.scale;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -639,8 +750,29 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     at[0].val.clusterDim.x = (unsigned)cg; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    if (cg == 2) VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_umma_kernel<2>, p));
-    else VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_umma_kernel<1>, p));
+    static const bool prof_on = getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';
+    if (prof_on) {
+        VO2W_CUDA_OK(cudaMalloc(&p.prof, (size_t)grid * 16 * 8));
+        VO2W_CUDA_OK(cudaMemsetAsync(p.prof, 0, (size_t)grid * 16 * 8, st));
+    }
+    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C), p));
+    if (prof_on) {   // debug aid: per-role cycle accounting, averaged over the CTAs that recorded it
+        std::vector<unsigned long long> h((size_t)grid * 16);
+        VO2W_CUDA_OK(cudaStreamSynchronize(st));
+        VO2W_CUDA_OK(cudaMemcpy(h.data(), p.prof, h.size() * 8, cudaMemcpyDeviceToHost));
+        cudaFree(p.prof);
+        double a[10] = {0};
+        int nl = 0;
+        for (int b = 0; b < grid; ++b) {
+            if (h[(size_t)b * 16]) ++nl;
+            for (int i = 0; i < 10; ++i) a[i] += (double)h[(size_t)b * 16 + i];
+        }
+        const double dl = nl ? nl : 1, dg = grid;
+        fprintf(stderr, "[pair prof] C=%d segs=%d k0=%d NB=%d iters=%d tiles=%d | mma total %.0f: wait xa %.0f w %.0f t %.0f d2e %.0f | "
+                        "e1 wait %.0f work %.0f (tmem ld+wait %.0f) | e2 wait %.0f work %.0f (cycles per CTA)\n",
+                p.C, p.n_seg, p.seg[0].k, p.NB, p.iters, p.n_tiles, a[0] / dl, a[1] / dl, a[2] / dl, a[3] / dl, a[4] / dl,
+                a[5] / dg, a[6] / dg, a[9] / dg, a[7] / dg, a[8] / dg);
+    }
     return VO2W_OK;
 }
 

@@ -7,12 +7,18 @@
 
 #include "common.cuh"
 
-// warp roles: 0 input-tile producer, 1 MMA issuer / peer relay, 2 weight producer, 3 TMEM owner,
-//             4-7 epilogue 1 (conv1 accumulators -> conv2 operand in shared memory),
-//             8-15 epilogue 2 (conv2 accumulators + residuals -> HBM); TMEM lane quarter = warp & 3
+// warp roles:
+//   0-7   epilogue 2 (conv2 accumulators + residuals -> HBM), two warps per TMEM lane quarter (= warp & 3)
+//   8-11  epilogue 1 (conv1 accumulators -> conv2 operand in shared memory)
+//   12 input-tile producer, 13 weight producer, 14 TMEM owner, 15 MMA issuer (leader CTA) / relay (peer CTA)
 #define PAIR_THREADS 512
-#define PAIR_E1_WARPS 4
 #define PAIR_E2_WARPS 8
+#define PAIR_E1_WARP0 8
+#define PAIR_E1_WARPS 4
+#define PAIR_WARP_XA 12
+#define PAIR_WARP_W 13
+#define PAIR_WARP_TMEM 14
+#define PAIR_WARP_MMA 15
 #define PAIR_MAX_SLOTS 4
 #define PAIR_MAX_SEG 3
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
@@ -20,11 +26,11 @@
 struct PairSegP {
     const __nv_bfloat16* xa;      // conv1 operand = leaky_relu(x, 0.1) as bf16, [B][C/8][Lp][8], zero pad rows
     const __nv_bfloat16* x;       // residual stream x as raw bf16, same layout
-    const uint8_t* w1;            // packed conv1 weights: [cta rank][item = tap*kbs + kb][KB/8][C/CG][8] bf16
+    const uint8_t* w1;            // packed conv1: [cta rank][item][KB/8][C/CG][8] bf16, item 0 = bias, item 1 + tap*kbs + kb = weights
     const uint8_t* w2;
     int32_t k, dil;               // conv1: k taps, dilation dil; conv2: k taps, dilation 1
     int32_t h1, h2;               // halos: dil*(k-1)/2 and (k-1)/2
-    int32_t n_items;              // k * (C / KB)
+    int32_t n_items;              // 1 + k * (C / KB)
     int32_t xa_rows;              // 128*NB + 2*h1
     uint32_t conv_bytes_rank;     // bytes of one packed conv per CTA rank
     uint32_t pad_;
@@ -35,7 +41,6 @@ struct PairP {
     int32_t n_seg;
     __nv_bfloat16* out_raw;       // optional: y * scale as bf16 (the stream for the next iteration)
     __nv_bfloat16* out_act;       // leaky_relu(bf16(y * scale), out_slope) as bf16 (operand of the next layer)
-    const float* bias;            // [n_seg][C] conv1 biases, then [C] = sum over segments of the conv2 biases
     int32_t C, L, Lp;
     int32_t h2max;
     int32_t NB;                   // 128-row accumulator blocks per CTA tile
@@ -46,8 +51,9 @@ struct PairP {
     int32_t KB, ksteps, kbs_log2; // input channels per item, K=16 steps per item, log2(C / KB)
     int32_t items_per_stage, n_slots;
     uint32_t item_bytes, stage_bytes;
-    uint32_t xa_off[2], t_off, ring_off, bias_off;   // byte offsets into dynamic shared memory
+    uint32_t xa_off[2], t_off, ring_off, ones_off;   // byte offsets into dynamic shared memory
     uint32_t smem_bytes;
+    unsigned long long* prof;     // optional [grid][16] cycle counters (VO2W_PAIR_PROF=1), else null
 };
 
 // Weights of one ResBlock iteration (convs1[m], convs2[m]) packed for the kernel.
@@ -55,14 +61,12 @@ struct PackedPair {
     int C = 0, k = 0, dil = 1, cg = 1;
     uint8_t* w1_dev = nullptr;
     uint8_t* w2_dev = nullptr;
-    std::vector<float> b1, b2;    // host copies (a launch group concatenates them)
 };
 
 // What one launch runs: 1..3 iterations whose results are summed.
 struct PackedGroup {
     int n_seg = 0;
     const PackedPair* seg[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
-    float* bias_dev = nullptr;    // [n_seg][C] + [C]
 };
 
 struct PairIO {
@@ -81,8 +85,9 @@ int pack_pair(PackedPair& P, const float* w1, const float* b1, const float* w2, 
 void free_pair(PackedPair& P);
 int make_group(PackedGroup& G, const PackedPair* const* pairs, int n_seg);
 void free_group(PackedGroup& G);
-// host-side layout of one conv ([rank][item][chunk][n_local][8] bf16 bits); exposed for the CPU tests
-void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, int C, int k, int cg);
+// host-side layout of one conv ([rank][item][chunk][n_local][8] bf16 bits, item 0 = bias as bf16 hi/lo in K
+// columns 0/1); exposed for the CPU tests
+void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, const float* bias, int C, int k, int cg);
 // fills the geometry of a launch (no pointers); returns the grid size or a negative error
 int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms);
 int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st);
