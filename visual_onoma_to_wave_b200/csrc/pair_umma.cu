@@ -146,8 +146,8 @@ enum {
     BAR_W_EMPTY = BAR_W_FULL + PAIR_MAX_SLOTS,
     BAR_W_FULL_PEER = BAR_W_EMPTY + PAIR_MAX_SLOTS,   // leader only
     BAR_D1_FULL = BAR_W_FULL_PEER + PAIR_MAX_SLOTS,   // conv1 accumulators complete
-    BAR_T_FULL,                                       // leader only: conv2 operand written by every e1 warp of the pair
-    BAR_D2_FULL,
+    BAR_T_FULL,                                       // [4] leader only: 64-channel block kb of the conv2 operand written
+    BAR_D2_FULL = BAR_T_FULL + 4,                     //     by every e1 warp of the pair
     BAR_D2_EMPTY,                                     // leader only: every e2 warp of the pair has read D2
     BAR_COUNT
 };
@@ -188,15 +188,16 @@ __device__ __forceinline__ void mma_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t 
 // second: reads the conv2 operand buffer (dilation 1; block c > 0 starts at row c*128 - 2*h2max).
 // keep:   accumulate on top of what the accumulators hold (conv2 of segments after the first).
 // The whole warp walks the (warp-uniform) loops so that addresses stay in uniform registers; one elected
-// lane issues.  All descriptor arithmetic is in 16-byte units on the low descriptor word.
-template <int CG, int NB, int KS>
-__device__ __forceinline__ void issue_conv(const PairP& p, uint32_t bar0, uint32_t a_addr, uint32_t a_rows, int n_items,
+// lane issues.  NI issuer warps split the row blocks (issue, not execution, limits the small-N stages).  All descriptor arithmetic is in 16-byte units on the low descriptor word.
+template <int CG, int NB, int KS, int NI>
+__device__ __forceinline__ void issue_conv(const PairP& p, int issuer, uint32_t bar0, uint32_t a_addr, uint32_t a_rows, int n_items,
                                            int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
-                                           uint32_t idesc, uint32_t ones_lo, uint32_t& wit, long long& w_wait) {
+                                           uint32_t idesc, uint32_t ones_lo, uint32_t& wit, long long& w_wait,
+                                           int k_taps, uint32_t t_parity, long long& t_wait) {
     const uint32_t n_loc = (uint32_t)p.C / CG;
     const uint32_t a_base = ((a_addr >> 4) & 0x3FFFu) | (a_rows << 16);      // LBO = a_rows * 16 B
     const uint32_t b_lbo_field = n_loc << 16;                                 // LBO = n_loc * 16 B
-    const int kbs_mask = (1 << p.kbs_log2) - 1;
+    uint32_t tap = 0, kb = 0;                                                 // items 1.. run kb-major: (kb, tap)
     const uint32_t kb_rows = ((uint32_t)p.KB >> 3) * a_rows;                  // 16-byte units per 64-channel block
     const uint32_t blk_back = second ? 2u * (uint32_t)p.h2max : 0u;
     const uint32_t item_units = p.item_bytes >> 4;
@@ -218,17 +219,26 @@ __device__ __forceinline__ void issue_conv(const PairP& p, uint32_t bar0, uint32
                 // item 0 is the bias: D = ones[128 x 16] . (b_hi, b_lo, 0, ...)^T initialises the accumulators
                 if (elect_one()) {
 #pragma unroll
-                    for (int blk = 0; blk < NB; ++blk)
-                        mma_lo<CG>(d_tmem + (uint32_t)(blk * p.C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
+                    for (int bi = 0; bi < NB / NI; ++bi)
+                        mma_lo<CG>(d_tmem + (uint32_t)((issuer + bi * NI) * p.C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
                 }
                 __syncwarp();
                 continue;
             }
-            const uint32_t tap = (uint32_t)((idx - 1) >> p.kbs_log2), kb = (uint32_t)((idx - 1) & kbs_mask);
+            if (second && tap == 0) {
+                // conv2 reads channel block kb of the operand buffer: wait until e1 has written it (the later
+                // blocks are still being converted while these MMAs run)
+                const long long tt = clock64();
+                mbar_wait_cluster(bar0 + 8u * (BAR_T_FULL + kb), t_parity);
+                t_wait += clock64() - tt;
+                __syncwarp();
+                tc_fence_after();
+            }
             const uint32_t a_lo = a_base + kb * kb_rows + tap * (uint32_t)dil;
             if (elect_one()) {
 #pragma unroll
-                for (int blk = 0; blk < NB; ++blk) {
+                for (int bi = 0; bi < NB / NI; ++bi) {
+                    const int blk = issuer + bi * NI;                       // this issuer's row blocks
                     const uint32_t a_blk = a_lo + (uint32_t)(blk * 128) - (blk > 0 ? blk_back : 0u);
 #pragma unroll
                     for (int s = 0; s < KS; ++s)
@@ -237,6 +247,7 @@ __device__ __forceinline__ void issue_conv(const PairP& p, uint32_t bar0, uint32
                 }
             }
             __syncwarp();
+            if (++tap == (uint32_t)k_taps) { tap = 0; ++kb; }
         }
         if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
         __syncwarp();
@@ -251,6 +262,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
     constexpr int KS = C < 64 ? 2 : 4;                       // K=16 steps per weight item (64 input channels, 32 for C=32)
     constexpr int GROUPS = C / 32;                           // 32 accumulator columns per tcgen05.ld
     constexpr int CHUNKS = C / 8;
+    constexpr int NI = NB >= 2 ? 2 : 1;                      // MMA issuer warps
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[BAR_COUNT];
     __shared__ uint32_t tmem_base_s;
@@ -263,7 +275,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < BAR_COUNT; ++i)
-            mbar_init(bar0 + 8u * i, i == BAR_T_FULL ? CG * PAIR_E1_WARPS : (i == BAR_D2_EMPTY ? CG * PAIR_E2_WARPS : 1));
+            {
+            const bool by_issuers = (i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 2) || (i >= BAR_W_EMPTY && i < BAR_W_EMPTY + PAIR_MAX_SLOTS) ||
+                                    i == BAR_D1_FULL || i == BAR_D2_FULL;     // one tcgen05.commit per issuer warp
+            mbar_init(bar0 + 8u * i, (i >= BAR_T_FULL && i < BAR_T_FULL + 4) ? CG * PAIR_E1_WARPS
+                                     : (i == BAR_D2_EMPTY ? CG * PAIR_E2_WARPS : (by_issuers ? NI : 1)));
+        }
         fence_mbar_init();
     }
     if (warp == PAIR_WARP_TMEM) tmem_alloc_cg<CG>(smem_u32(&tmem_base_s), 512u);
@@ -327,15 +344,16 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
             }
         }
-    } else if (warp == PAIR_WARP_MMA) {
-        if (rank == 0) {
+    } else if (warp >= PAIR_WARP_MMA0 && warp < PAIR_WARP_MMA0 + NI && rank == 0) {
+        {
+            const int issuer = warp - PAIR_WARP_MMA0;
             // ================= MMA issuer (whole warp loops, one elected lane issues) =================
             const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
             const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
             const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(NB * C);
             uint32_t wit = 0;
             int n = 0;
-            long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0;
+            long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0, c_drain = 0;
             const long long c_start = clock64();
             for (int it = 0; it < p.iters; ++it) {
                 for (int s = 0; s < n_seg; ++s, ++n) {
@@ -346,36 +364,40 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
                     c_xa += clock64() - c0;
                     tc_fence_after();
-                    issue_conv<CG, NB, KS>(p, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false, d1,
-                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w);
+                    issue_conv<CG, NB, KS, NI>(p, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false, d1,
+                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, c_t);
                     if (elect_one()) {
                         mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));   // input tile reusable
                         mma_commit<CG>(bar0 + 8u * BAR_D1_FULL);            // e1 may start
                     }
                     __syncwarp();
-                    // conv2 operand written by all e1 warps of the pair; D2 drained by the previous tile's e2
-                    c0 = clock64();
-                    mbar_wait_cluster(bar0 + 8u * BAR_T_FULL, (uint32_t)(n & 1));
-                    c_t += clock64() - c0;
+                    if (p.prof) {   // profiling only: how long the tensor pipe still runs after the last issue
+                        const long long cd = clock64();
+                        mbar_wait(bar0 + 8u * BAR_D1_FULL, (uint32_t)(n & 1));
+                        c_drain += clock64() - cd;
+                    }
+                    // D2 drained by the previous tile's e2 (the operand buffer is awaited per channel block inside)
                     c0 = clock64();
                     if (s == 0 && it > 0) mbar_wait_cluster(bar0 + 8u * BAR_D2_EMPTY, (uint32_t)((it - 1) & 1));
                     c_d2 += clock64() - c0;
                     tc_fence_after();
-                    issue_conv<CG, NB, KS>(p, bar0, sm0 + p.t_off, (uint32_t)p.t_rows, sg.n_items, 1, true, s > 0, d2,
-                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w);
+                    issue_conv<CG, NB, KS, NI>(p, issuer, bar0, sm0 + p.t_off, (uint32_t)p.t_rows, sg.n_items, 1, true, s > 0, d2,
+                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, (uint32_t)(n & 1), c_t);
                     if (s == n_seg - 1) {
                         if (elect_one()) mma_commit<CG>(bar0 + 8u * BAR_D2_FULL);
                         __syncwarp();
                     }
                 }
             }
-            if (p.prof && lane == 0) {
+            if (p.prof && lane == 0 && issuer == 0) {
                 unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
                 o[0] = (unsigned long long)(clock64() - c_start);
                 o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
-                o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2;
+                o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2; o[10] = (unsigned long long)c_drain;
             }
-        } else if (lane == 0) {
+        }
+    } else if (warp == PAIR_WARP_MMA0 && rank != 0) {
+        if (lane == 0) {
             // ================= peer relay: forward "landed" events to the leader's barriers =================
             uint32_t wit = 0;
             int n = 0;
@@ -402,7 +424,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const int q4 = warp & 3;                         // TMEM lane quarter this warp may read
         const int q = q4 * 32 + lane;                    // row inside a 128-row block
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        const uint32_t t_full_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_T_FULL, 0) : 0u;
+        const uint32_t t_full_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_T_FULL, 0) : bar0 + 8u * BAR_T_FULL;
+        constexpr int UNITS_PER_KB = (C < 64 ? 1 : 2) * NB;   // 32-column groups per weight channel block x row blocks
         const __nv_bfloat162 slope2 = __floats2bfloat162_rn(0.1f, 0.1f);
         const uint32_t t_row0 = sm0 + p.t_off + (uint32_t)q * 16u;
         // convert 32 accumulator columns of one row block: bf16, leaky-relu, 4 x 16-byte stores
@@ -443,15 +466,19 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     const int r0 = t0 + b0 * 128, r1 = t0 + b1 * 128;      // conv2 zero-pads outside the utterance
                     convert(ra, g0, b0, r0 >= 0 && r0 < p.L);
                     convert(rb, g1, b1, r1 >= 0 && r1 < p.L);
+                    if ((u + 2) % UNITS_PER_KB == 0) {
+                        // channel block (u + 1) / UNITS_PER_KB of the operand is complete for this warp's rows
+                        fence_proxy_async();             // generic-proxy stores -> visible to the tensor core (async proxy)
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            const uint32_t bar = t_full_addr + 8u * (uint32_t)((u + 1) / UNITS_PER_KB);
+                            if (CG == 2) mbar_arrive_remote(bar);
+                            else mbar_arrive(bar);
+                        }
+                    }
                 }
                 const long long c2 = clock64();
-                fence_proxy_async();                     // generic-proxy stores -> visible to the tensor core (async proxy)
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) {
-                    if (CG == 2) mbar_arrive_remote(t_full_addr);
-                    else mbar_arrive(bar0 + 8u * BAR_T_FULL);
-                }
                 c_work += clock64() - c1;
                 c_fence += clock64() - c2;
             }
@@ -609,8 +636,8 @@ void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, const float
             out[o + (size_t)n * 8 + 1] = f32_to_bf16_rn(b - hf);
         }
         o += item;
-        for (int tap = 0; tap < k; ++tap)
-            for (int kb = 0; kb < kbs; ++kb)
+        for (int kb = 0; kb < kbs; ++kb)
+            for (int tap = 0; tap < k; ++tap)
                 for (int chunk = 0; chunk < KB / 8; ++chunk)
                     for (int n = 0; n < n_loc; ++n)
                         for (int e = 0; e < 8; ++e) {
@@ -761,16 +788,16 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
         VO2W_CUDA_OK(cudaStreamSynchronize(st));
         VO2W_CUDA_OK(cudaMemcpy(h.data(), p.prof, h.size() * 8, cudaMemcpyDeviceToHost));
         cudaFree(p.prof);
-        double a[10] = {0};
+        double a[11] = {0};
         int nl = 0;
         for (int b = 0; b < grid; ++b) {
             if (h[(size_t)b * 16]) ++nl;
-            for (int i = 0; i < 10; ++i) a[i] += (double)h[(size_t)b * 16 + i];
+            for (int i = 0; i < 11; ++i) a[i] += (double)h[(size_t)b * 16 + i];
         }
         const double dl = nl ? nl : 1, dg = grid;
-        fprintf(stderr, "[pair prof] C=%d segs=%d k0=%d NB=%d iters=%d tiles=%d | mma total %.0f: wait xa %.0f w %.0f t %.0f d2e %.0f | "
+        fprintf(stderr, "[pair prof] C=%d segs=%d k0=%d NB=%d iters=%d tiles=%d | mma total %.0f: wait xa %.0f w %.0f t %.0f d2e %.0f drain1 %.0f | "
                         "e1 wait %.0f work %.0f (tmem ld+wait %.0f) | e2 wait %.0f work %.0f (cycles per CTA)\n",
-                p.C, p.n_seg, p.seg[0].k, p.NB, p.iters, p.n_tiles, a[0] / dl, a[1] / dl, a[2] / dl, a[3] / dl, a[4] / dl,
+                p.C, p.n_seg, p.seg[0].k, p.NB, p.iters, p.n_tiles, a[0] / dl, a[1] / dl, a[2] / dl, a[3] / dl, a[4] / dl, a[10] / dl,
                 a[5] / dg, a[6] / dg, a[9] / dg, a[7] / dg, a[8] / dg);
     }
     return VO2W_OK;

@@ -10,15 +10,15 @@
 // warp roles:
 //   0-7   epilogue 2 (conv2 accumulators + residuals -> HBM), two warps per TMEM lane quarter (= warp & 3)
 //   8-11  epilogue 1 (conv1 accumulators -> conv2 operand in shared memory)
-//   12 input-tile producer, 13 weight producer, 14 TMEM owner, 15 MMA issuer (leader CTA) / relay (peer CTA)
+//   12 input-tile producer, 13 weight producer + TMEM owner, 14-15 MMA issuers (leader CTA; 14 = relay in the peer CTA)
 #define PAIR_THREADS 512
 #define PAIR_E2_WARPS 8
 #define PAIR_E1_WARP0 8
 #define PAIR_E1_WARPS 4
 #define PAIR_WARP_XA 12
 #define PAIR_WARP_W 13
-#define PAIR_WARP_TMEM 14
-#define PAIR_WARP_MMA 15
+#define PAIR_WARP_TMEM 13
+#define PAIR_WARP_MMA0 14
 #define PAIR_MAX_SLOTS 4
 #define PAIR_MAX_SEG 3
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
@@ -26,7 +26,7 @@
 struct PairSegP {
     const __nv_bfloat16* xa;      // conv1 operand = leaky_relu(x, 0.1) as bf16, [B][C/8][Lp][8], zero pad rows
     const __nv_bfloat16* x;       // residual stream x as raw bf16, same layout
-    const uint8_t* w1;            // packed conv1: [cta rank][item][KB/8][C/CG][8] bf16, item 0 = bias, item 1 + tap*kbs + kb = weights
+    const uint8_t* w1;            // packed conv1: [cta rank][item][KB/8][C/CG][8] bf16, item 0 = bias, item 1 + kb*k + tap = weights
     const uint8_t* w2;
     int32_t k, dil;               // conv1: k taps, dilation dil; conv2: k taps, dilation 1
     int32_t h1, h2;               // halos: dil*(k-1)/2 and (k-1)/2
