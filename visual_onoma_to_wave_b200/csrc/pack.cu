@@ -166,11 +166,14 @@ int launch_layers(const PackedLayer* const* layers, const __nv_bfloat16* const* 
     p.a_bytes = (uint32_t)(p.Cin * rows_max * 2);
     const int steps = p.Cin / 16;
     int ks = 0;
-    for (int c = std::min(steps, 8); c >= 1; --c) {
-        if (steps % c) continue;
-        const size_t stage = (size_t)n_max * 32 * c;
-        if (stage <= 48 * 1024 && p.a_bytes + UMMA_STAGES * stage <= UMMA_SMEM_LIMIT) { ks = c; break; }
-    }
+    // prefer a footprint that lets two CTAs share an SM (their copy / MMA / epilogue phases then overlap)
+    const size_t limits[2] = {110 * 1024, UMMA_SMEM_LIMIT};
+    for (int pass = 0; pass < 2 && !ks; ++pass)
+        for (int c = std::min(steps, 8); c >= 1; --c) {
+            if (steps % c) continue;
+            const size_t stage = (size_t)n_max * 32 * c;
+            if (stage <= 48 * 1024 && p.a_bytes + UMMA_STAGES * stage <= limits[pass]) { ks = c; break; }
+        }
     VO2W_REQUIRE(ks > 0, "launch_layers: tile does not fit shared memory (Cin %d rows %d)", p.Cin, rows_max);
     p.kb_steps = ks;
     p.n_kblocks = steps / ks;
