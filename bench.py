@@ -265,7 +265,7 @@ def run_ours(args):
         except Exception as e:  # reported, not fatal for the vocoder metric
             extra["length_regulator"] = {"error": str(e)}
         if world == 1 and not args.no_cpu_baseline:
-            n_cpu = 4
+            n_cpu = 64
             audio_s, times = cpu_generator_rate(n_cpu, reps=2, warm=1)
             cpu_baseline = {"value": audio_s / min(times), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                             "sample": f"{n_cpu} of the {N_UTT} utterances x {T_FRAMES} frames, best of 2 after 1 warm-up "
@@ -301,7 +301,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--sub-batch", type=int, default=64)
-    ap.add_argument("--ref-utts", type=int, default=4, help="utterances per step of the CPU arm (bounded sample)")
+    ap.add_argument("--ref-utts", type=int, default=16, help="utterances per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
