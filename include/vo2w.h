@@ -110,12 +110,14 @@ int vo2w_debug_layer(int transposed, int use_umma, const float* w_host, const fl
                      const float* res_dev, float* out_dev, void* stream);
 
 /* Known-answer probe of the fused ResBlock-iteration kernel (scripts/hifigan/models.py:97-103, 154-160):
- *   y   = scale * sum_{s < n_seg} [ x_s + conv2_s(leaky_relu(conv1_s(leaky_relu(x_s, 0.1)), 0.1)) ]
- *   out = bf16(y)  (optional),  act = leaky_relu(out, out_slope)
+ *   y   = scale * sum_{s < n_seg} [ x'_s + conv2_s(leaky_relu(conv1_s(a_s), 0.1)) ],  a_s = bf16(leaky_relu(x_s, 0.1))
+ *   act = bf16(leaky_relu(y, out_slope))   (the only tensor the kernel leaves in HBM)
+ *   out = act >= 0 ? act : act / out_slope (optional: the value a consumer recovers from the stream)
+ * where x'_s = a_s >= 0 ? a_s : 10 a_s is the residual as the kernel recovers it from its input stream.
  * conv1_s = Conv1d(C,C,ks[s],dilation=dils[s]), conv2_s = Conv1d(C,C,ks[s]), both "same"-padded, weights and
  * biases in the torch layout on the host (arrays of n_seg pointers); x_s / out / act NCL fp32 on the device.
  * n_seg = 1, scale = 1 is one ResBlock iteration; n_seg = num_kernels, scale = 1/num_kernels the MRF
- * average of a stage.  The kernel keeps x_s in bf16 (the HBM format of the bf16 mode).
+ * average of a stage.
  * cg = CTAs per tcgen05 group (1, or 2 for cta_group::2 pairs). */
 int vo2w_debug_pair(int n_seg, const float* const* w1_host, const float* const* b1_host,
                     const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
@@ -132,6 +134,13 @@ int vo2w_debug_pack(int transposed, const float* w, const float* bias, int Cin, 
 
 /* Kernel launches issued by the last forward (bench.py's gpu_launches). */
 int vo2w_generator_last_launches(const vo2w_generator* g);
+
+/* Per-launch device timing of a forward (measurement aid of bench.py's roofline): with timing on, every forward
+ * records a CUDA event on its stream around each launch.  get_timing waits for the last forward and fills
+ * ms[i] = duration of launch i and kind[i] = 0 layout helper / 1 single convolution / 2 fused ResBlock
+ * iterations (pair_umma_kernel); returns the number of launches or a negative error. */
+int vo2w_generator_set_timing(vo2w_generator* g, int on);
+int vo2w_generator_get_timing(vo2w_generator* g, float* ms, int32_t* kind, int capacity);
 
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad

@@ -123,3 +123,45 @@ def generator_forward_emulated_v2(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float3
         x = f32(F.conv1d(act(x, 0.01), W["conv_post.weight"], W["conv_post.bias"], padding=3))
         x = torch.tanh(x)
     return x.float()
+
+
+def generator_forward_emulated_v3(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float32, taps=None):
+    """Dataflow of the single-stream bf16 pipeline: the ONLY tensor a layer leaves in HBM is
+    s = bf16(leaky_relu(y_fp32, 0.1)), the next convolution's MMA operand.  A consumer that needs the
+    value itself (the residual add of ResBlock.forward, models.py:102) recovers it exactly-invertibly
+    from the stream: x = s if s >= 0 else 10 * s (an exact fp32 product of a bf16 number).  Compared with
+    v2 the operand is rounded once instead of twice and half of the HBM traffic disappears."""
+    sd = fold_weight_norm(sd)
+    W = {k: (_r(v.float(), "bf16") if k.endswith("weight") else v.float()).to(acc_dtype) for k, v in sd.items()}
+    nk = len(cfg["resblock_kernel_sizes"])
+    f32 = lambda t: t.float().to(acc_dtype)
+    b16 = lambda t: _r(t, "bf16")
+    stream = lambda t, s=LRELU_SLOPE: b16(F.leaky_relu(f32(t), s))         # fp32 value -> HBM stream
+    inv = lambda s: f32(torch.where(s < 0, s * 10.0, s))                   # stream -> value (slope 0.1 only)
+
+    with torch.no_grad():
+        s = stream(F.conv1d(b16(mel.to(acc_dtype)), W["conv_pre.weight"], W["conv_pre.bias"], padding=3))
+        for i, (u, k) in enumerate(zip(cfg["upsample_rates"], cfg["upsample_kernel_sizes"])):
+            s = stream(F.conv_transpose1d(s, W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u, padding=(k - u) // 2))
+            if taps is not None:
+                taps[f"ups.{i}"] = inv(s).float()
+            xs = None
+            for j, (rk, rd) in enumerate(zip(cfg["resblock_kernel_sizes"], cfg["resblock_dilation_sizes"])):
+                p = f"resblocks.{i * nk + j}"
+                sr = s
+                for m, d in enumerate(rd):
+                    t = f32(F.conv1d(sr, W[f"{p}.convs1.{m}.weight"], W[f"{p}.convs1.{m}.bias"],
+                                     padding=get_padding(rk, d), dilation=d))
+                    t = b16(F.leaky_relu(t, LRELU_SLOPE))
+                    y = f32(F.conv1d(t, W[f"{p}.convs2.{m}.weight"], W[f"{p}.convs2.{m}.bias"], padding=get_padding(rk, 1)))
+                    r = f32(y + inv(sr))
+                    if m < 2:
+                        sr = stream(r)
+                xs = r if xs is None else f32(xs + r)
+            last = i + 1 == len(cfg["upsample_rates"])
+            s = stream(xs * (1.0 / nk), 0.01 if last else LRELU_SLOPE)
+            if taps is not None:
+                taps[f"mrf_act.{i}"] = s.float()
+        x = f32(F.conv1d(s, W["conv_post.weight"], W["conv_post.bias"], padding=3))
+        x = torch.tanh(x)
+    return x.float()

@@ -160,6 +160,60 @@ def test_single_layer_against_torch(dev, case, umma):
 
 
 # ------------------------------------------------------------------------------------------
+# fused ResBlock iterations (known-answer against torch with the kernel's operand rounding)
+# ------------------------------------------------------------------------------------------
+PAIRS = [  # C, kernel sizes, dilations, B, L, cg
+    (32, [3], [1], 2, 700, 2), (32, [11], [5], 3, 1500, 2), (64, [7], [3], 2, 900, 2), (128, [3], [1], 2, 600, 2),
+    (128, [11], [5], 2, 1100, 2), (256, [3], [1], 2, 300, 2), (256, [7], [5], 3, 500, 2), (32, [7], [1], 1, 50, 2),
+    (64, [11], [1], 9, 3000, 2), (32, [3, 7, 11], [5, 5, 5], 3, 2000, 2), (64, [3, 7, 11], [5, 5, 5], 2, 1500, 2),
+    (128, [3, 7, 11], [5, 5, 5], 2, 1200, 2), (256, [3, 7, 11], [5, 5, 5], 2, 700, 2), (128, [3, 7], [5, 5], 2, 500, 1),
+    (64, [7], [3], 2, 900, 1),
+]
+
+
+def _b16(t):
+    return t.to(torch.bfloat16).to(t.dtype)
+
+
+@pytest.mark.parametrize("case", PAIRS, ids=lambda c: f"C{c[0]}-k{'_'.join(map(str, c[1]))}-d{c[2][0]}-B{c[3]}-L{c[4]}-cg{c[5]}")
+def test_fused_resblock_iterations_against_torch(dev, case):
+    """ResBlock.forward iteration(s) (models.py:97-103) and the MRF average (models.py:154-160) through
+    pair_umma_kernel.  Reference: the same dataflow in torch fp64 with the kernel's bf16 operand rounding."""
+    import ctypes as C
+    Cc, ks, ds, B, L, cg = case
+    n = len(ks)
+    slope = 0.01 if (n == 3 and Cc == 32) else 0.1
+    g = torch.Generator().manual_seed(Cc + 7 * ks[0])
+    w1 = [(torch.randn(Cc, Cc, k, generator=g) / (Cc * k) ** 0.5).contiguous() for k in ks]
+    w2 = [(torch.randn(Cc, Cc, k, generator=g) / (Cc * k) ** 0.5).contiguous() for k in ks]
+    b1 = [torch.randn(Cc, generator=g) * 0.1 for _ in ks]
+    b2 = [torch.randn(Cc, generator=g) * 0.1 for _ in ks]
+    x = [torch.randn(B, Cc, L, generator=g) for _ in ks]
+    xd = [t.to(dev) for t in x]
+    out = torch.full((B, Cc, L), float("nan"), device=dev)
+    act = torch.full((B, Cc, L), float("nan"), device=dev)
+    pa = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    scale = 1.0 / n
+    _lib.check(_lib.lib().vo2w_debug_pair(n, pa(w1), pa(b1), pa(w2), pa(b2), Cc, (C.c_int * n)(*ks), (C.c_int * n)(*ds), cg,
+                                          pa(xd), B, L, scale, slope, out.data_ptr(), act.data_ptr(), None))
+    ref = 0
+    for s in range(n):
+        xa = _b16(F.leaky_relu(x[s], 0.1)).double()            # the HBM stream
+        xr = torch.where(xa < 0, xa * 10.0, xa)                # residual recovered from it
+        t = F.conv1d(xa, _b16(w1[s]).double(), b1[s].double(), padding=ds[s] * (ks[s] - 1) // 2, dilation=ds[s])
+        t = _b16(F.leaky_relu(t.float(), 0.1)).double()
+        ref = ref + F.conv1d(t, _b16(w2[s]).double(), b2[s].double(), padding=(ks[s] - 1) // 2) + xr
+    aref = F.leaky_relu(ref * scale, slope)
+    got = act.cpu().double()
+    assert torch.isfinite(got).all()
+    # one bf16 ulp of the value, plus the effect of an intermediate landing on the other side of a bf16 rounding boundary
+    tol = aref.abs() * 2.0 ** -7 + 2e-2
+    assert int(((got - aref).abs() > tol).sum()) == 0, float((got - aref).abs().max())
+    inv = torch.where(got < 0, got / slope, got)
+    assert float((out.cpu().double() - inv).abs().max()) <= 1e-5 * float(inv.abs().max())
+
+
+# ------------------------------------------------------------------------------------------
 # whole Generator
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("case", ["a", "b", "c"])

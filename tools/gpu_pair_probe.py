@@ -11,12 +11,12 @@ def b16(t):
     return t.to(torch.bfloat16).to(t.dtype)
 
 def ref_iter(x, w1, b1, w2, b2, k, d):
-    xd = b16(x).double()                       # stream value in HBM is bf16
-    xa = b16(F.leaky_relu(xd, 0.1))
+    xa = b16(F.leaky_relu(x, 0.1)).double()    # the stream in HBM: bf16(leaky_relu(x))
+    xr = torch.where(xa < 0, xa * 10.0, xa)    # the residual as the kernel recovers it
     t = F.conv1d(xa, b16(w1).double(), b1.double(), padding=d * (k - 1) // 2, dilation=d)
-    t = b16(F.leaky_relu(b16(t.float()), 0.1).double())
+    t = b16(F.leaky_relu(t.float(), 0.1)).double()
     y = F.conv1d(t, b16(w2).double(), b2.double(), padding=(k - 1) // 2)
-    return y + xd
+    return y + xr
 
 def ptr_array(ts):
     return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
@@ -42,15 +42,16 @@ def run(Cc, ks, ds, cg, B, L, seed=0, slope=0.1):
     _lib.check(rc, "vo2w_debug_pair")
     torch.cuda.synchronize()
     ref = sum(ref_iter(x[s], w1[s], b1[s], w2[s], b2[s], ks[s], ds[s]) for s in range(n)).float() * scale
-    got = out.cpu()
-    err = (got - ref).abs()
-    tol = ref.abs() * 2.0 ** -7 + 2e-2          # one bf16 ulp of the value plus accumulation noise
+    aref = F.leaky_relu(ref, slope)
+    got = act.cpu()
+    err = (got - aref).abs()
+    tol = aref.abs() * 2.0 ** -7 + 2e-2   # one bf16 ulp of the value plus accumulation noise
     bad = int((err > tol).sum())
-    aref = b16(F.leaky_relu(got, slope))
-    aerr = (act.cpu() - aref).abs()
-    abad = int((aerr > aref.abs() * 2.0 ** -7 + 1e-6).sum())   # packed bf16 leaky-relu: within one ulp
+    inv = torch.where(got < 0, got / slope, got)
+    aerr = (out.cpu() - inv).abs()
+    abad = int((aerr > inv.abs() * 1e-6).sum())
     print(f"C={Cc:3d} k={ks} d={ds} cg={cg} B={B} L={L:6d}: max err {err.max().item():.4f} mean {err.mean().item():.5f} "
-          f"bad {bad} act max err {aerr.max().item():.2e} bad {abad}  ({time.time() - t0:.2f}s)", flush=True)
+          f"bad {bad} inverse max err {aerr.max().item():.2e} bad {abad}  ({time.time() - t0:.2f}s)", flush=True)
     if bad:
         idx = (err > tol).nonzero()
         print("   first bad:", idx[:5].tolist(), "rows(l) hist:", torch.bincount((idx[:, 2] // 64).clamp(max=40))[:41].tolist())

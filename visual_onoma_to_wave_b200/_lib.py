@@ -47,6 +47,8 @@ SYMBOLS = {
                                   C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                   C.c_void_p]),
     "vo2w_generator_last_launches": (C.c_int, [C.c_void_p]),
+    "vo2w_generator_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "vo2w_generator_get_timing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "vo2w_lr_lengths": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vo2w_length_regulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
                                        C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]),

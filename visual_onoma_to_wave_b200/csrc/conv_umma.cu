@@ -174,22 +174,14 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
                 *(float4*)(p.out_f32 + f_off) = make_float4(v[0], v[1], v[2], v[3]);
                 *(float4*)(p.out_f32 + f_off + f_step) = make_float4(v[4], v[5], v[6], v[7]);
             }
-            if (p.out_bf16 || p.out_raw) {
-                // HBM stream format of the bf16 mode: raw value rounded to bf16; the next layer's operand is
-                // leaky-relu of that ROUNDED value (what a consumer reading the stream would compute)
+            if (p.out_bf16) {
+                // HBM stream format of the bf16 mode: bf16(leaky_relu(value)) = the next layer's MMA operand; a
+                // consumer that needs the value itself inverts the activation (pair_umma.cu, e2)
                 __nv_bfloat162 h[4];
                 const size_t o = (((size_t)b * (p.Cout >> 3) + (co >> 3)) * p.Lp_out + VO2W_PAD_ROWS + lo) * 8;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-                if (p.out_raw) *(uint4*)(p.out_raw + o) = *(const uint4*)h;
-                if (p.out_bf16) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float2 f = __bfloat1622float2(h[i]);
-                        h[i] = __floats2bfloat162_rn(lrelu(f.x, p.out_slope), lrelu(f.y, p.out_slope));
-                    }
-                    *(uint4*)(p.out_bf16 + o) = *(const uint4*)h;
-                }
+                for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(lrelu(v[2 * i], p.out_slope), lrelu(v[2 * i + 1], p.out_slope));
+                *(uint4*)(p.out_bf16 + o) = *(const uint4*)h;
             }
             }   // !out_wave
             }   // valid

@@ -48,8 +48,7 @@ struct UConv {
     int32_t n_res;
     float div;                 // 1 or num_kernels (x = xs / 3)
     float* out_f32;            // optional [B][Cout/4][L_out][4]
-    __nv_bfloat16* out_bf16;   // optional operand buffer of the next layer: leaky-relu(out_slope) of the bf16-rounded value
-    __nv_bfloat16* out_raw;    // optional raw stream value as bf16, operand-buffer layout (residual of the ResBlocks)
+    __nv_bfloat16* out_bf16;   // optional operand buffer of the next layer: bf16(leaky_relu(value, out_slope)), the HBM stream
     float out_slope;
     float* out_wave;           // optional [B][L_out]: tanh(column 0)   (conv_post)
     int32_t Cout;              // channels of the output tensor
@@ -63,6 +62,7 @@ struct UConv {
 int umma_conv_launch(const UConv& p, int m_tiles, int n_tiles, int B, cudaStream_t st);
 size_t umma_conv_smem(const UConv& p);
 int pack_ncl_to_operand(const float* x, __nv_bfloat16* out, int B, int C, int L, int Lp, float slope, cudaStream_t st);
-int unchunk_bf16(const __nv_bfloat16* x, float* out, int B, int C, int L, int Lp, cudaStream_t st);
+// inv_slope != 1: undo the stream's leaky-relu (negative values are multiplied by inv_slope)
+int unchunk_bf16(const __nv_bfloat16* x, float* out, int B, int C, int L, int Lp, cudaStream_t st, float inv_slope = 1.0f);
 int unchunk_f32(const float* x, float* out, int B, int Cp, int C, int L, cudaStream_t st);
 int chunk_f32(const float* x, float* out, int B, int C, int Cp, int L, cudaStream_t st);

@@ -27,9 +27,10 @@ struct StageBufs {         // per upsampling stage, offsets in bytes into the wo
     int C = 0;
     long long L = 0, Lp = 0;
     // bf16 mode: operand-layout buffers [B][C/8][Lp][8]
-    size_t x = 0, xa = 0;          // ups output: raw stream value, leaky-relu(0.1) of it
-    size_t r[3][2] = {};           // stream of ResBlock j after iteration 0 / 1 (raw)
-    size_t ra[3][2] = {};          // leaky-relu(0.1) of it
+    // every tensor is a "stream": bf16(leaky_relu(value, 0.1)) = the next conv's MMA operand; the value itself
+    // (the residual of ResBlock.forward) is recovered from it by the consumer
+    size_t xa = 0;                 // ups output
+    size_t ra[3][2] = {};          // ResBlock j after iteration 0 / 1
     size_t mrf = 0;                // leaky-relu(xs / num_kernels) = operand of the next layer
     // fp32 mode (NCL)
     size_t x_f32 = 0, rr = 0, tt = 0, xs = 0;
@@ -62,6 +63,10 @@ struct vo2w_generator {
     Plan last;
     void* last_ws = nullptr;
     int last_launches = 0;
+    // optional per-launch device timing (vo2w_generator_set_timing): events around every launch of a forward
+    bool timing = false;
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> ev_kind;     // kind of the launch that ENDS at event i + 1
 };
 
 namespace {
@@ -98,11 +103,9 @@ Plan make_plan(const vo2w_generator* g, int B, int T) {
             s.L = L;
             s.Lp = vo2w_padded_len(L);
             const size_t bfb = (size_t)B * s.C * s.Lp * 2;
-            s.x = take(bfb);
             s.xa = take(bfb);
             for (int j = 0; j < g->nk; ++j)
                 for (int m = 0; m < 2; ++m) {
-                    s.r[j][m] = take(bfb);
                     s.ra[j][m] = take(bfb);
                 }
             s.mrf = take(bfb);
@@ -225,6 +228,7 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
 extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
     if (!g) return VO2W_OK;
     if (g->w_dev) cudaFree(g->w_dev);
+    for (cudaEvent_t e : g->ev) cudaEventDestroy(e);
     free_layer(g->conv_pre);
     free_layer(g->conv_post);
     for (int i = 0; i < 4; ++i) free_layer(g->ups[i]);
@@ -244,12 +248,46 @@ extern "C" size_t vo2w_generator_workspace_bytes(const vo2w_generator* g, int B,
 
 extern "C" int vo2w_generator_last_launches(const vo2w_generator* g) { return g ? g->last_launches : 0; }
 
+extern "C" int vo2w_generator_set_timing(vo2w_generator* g, int on) {
+    VO2W_REQUIRE(g, "generator_set_timing: null handle");
+    g->timing = on != 0;
+    return VO2W_OK;
+}
+
+extern "C" int vo2w_generator_get_timing(vo2w_generator* g, float* ms, int32_t* kind, int capacity) {
+    VO2W_REQUIRE(g && ms && kind, "generator_get_timing: null argument");
+    VO2W_REQUIRE(g->timing && (int)g->ev.size() > g->last_launches, "generator_get_timing: no timed forward has run");
+    const int n = g->last_launches;
+    VO2W_REQUIRE(n <= capacity, "generator_get_timing: %d launches, capacity %d", n, capacity);
+    VO2W_CUDA_OK(cudaEventSynchronize(g->ev[n]));
+    for (int i = 0; i < n; ++i) {
+        VO2W_CUDA_OK(cudaEventElapsedTime(&ms[i], g->ev[i], g->ev[i + 1]));
+        kind[i] = g->ev_kind[i];
+    }
+    return n;
+}
+
 // ---------------------------------------------------------------------------------------
 // forward schedules
 // ---------------------------------------------------------------------------------------
 namespace {
 
-#define VO2W_RUN(expr) do { int _rc = (expr); if (_rc != VO2W_OK) return _rc; ++g->last_launches; } while (0)
+// kind: 0 = layout / conversion helper, 1 = single convolution (umma_conv_kernel / fp32 kernels), 2 = fused ResBlock iterations
+int mark_launch(vo2w_generator* g, int kind, cudaStream_t st) {
+    ++g->last_launches;
+    if (!g->timing) return VO2W_OK;
+    while ((int)g->ev.size() <= g->last_launches) {
+        cudaEvent_t e;
+        VO2W_CUDA_OK(cudaEventCreate(&e));
+        g->ev.push_back(e);
+    }
+    g->ev_kind.resize(g->ev.size(), 0);
+    g->ev_kind[g->last_launches - 1] = kind;
+    VO2W_CUDA_OK(cudaEventRecord(g->ev[g->last_launches], st));
+    return VO2W_OK;
+}
+#define VO2W_RUNK(kind, expr) do { int _rc = (expr); if (_rc != VO2W_OK) return _rc; _rc = mark_launch(g, kind, st); if (_rc != VO2W_OK) return _rc; } while (0)
+#define VO2W_RUN(expr) VO2W_RUNK(1, expr)
 
 // Generator.forward (models.py:149-165) on the tcgen05 path.
 int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
@@ -257,7 +295,7 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
     auto bf = [&](size_t off) { return (__nv_bfloat16*)(ws + off); };
 
     // mel [B,80,T] fp32 -> operand buffer
-    VO2W_RUN(pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
+    VO2W_RUNK(0, pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
     {   // x = conv_pre(mel); the only consumer is leaky_relu(0.1) -> ups[0]
         const PackedLayer* L[1] = {&g->conv_pre};
         const __nv_bfloat16* in[1] = {bf(p.melb)};
@@ -274,7 +312,6 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             const PackedLayer* L[1] = {&g->ups[i]};
             const __nv_bfloat16* in[1] = {stage_in};
             EpilogueSpec ep;
-            ep.out_raw = bf(s.x);
             ep.out_bf16 = bf(s.xa);
             ep.out_slope = 0.1f;
             VO2W_RUN(launch_layers(L, in, 1, B, (int)L_in, ep, st));
@@ -286,11 +323,9 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             for (int m = 0; m < 2; ++m) {   // one ResBlock iteration per launch (models.py:97-103)
                 PairIO io;
                 io.xa[0] = m == 0 ? bf(s.xa) : bf(s.ra[j][0]);
-                io.x[0] = m == 0 ? bf(s.x) : bf(s.r[j][0]);
-                io.out_raw = bf(s.r[j][m]);
                 io.out_act = bf(s.ra[j][m]);
                 io.out_slope = 0.1f;
-                VO2W_RUN(pair_launch(g->iter_group[n][m], io, B, (int)s.L, st));
+                VO2W_RUNK(2, pair_launch(g->iter_group[n][m], io, B, (int)s.L, st));
             }
         }
         {   // last iteration of every ResBlock + xs = sum_j resblocks[j](x); x = xs / num_kernels (models.py:154-160)
@@ -298,12 +333,11 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             PairIO io;
             for (int j = 0; j < g->nk; ++j) {
                 io.xa[j] = bf(s.ra[j][1]);
-                io.x[j] = bf(s.r[j][1]);
             }
             io.out_act = bf(s.mrf);
             io.out_slope = next_slope;
             io.scale = 1.0f / (float)g->nk;
-            VO2W_RUN(pair_launch(g->mrf_group[i], io, B, (int)s.L, st));
+            VO2W_RUNK(2, pair_launch(g->mrf_group[i], io, B, (int)s.L, st));
         }
         stage_in = bf(s.mrf);
         L_in = s.L;
@@ -405,6 +439,14 @@ extern "C" int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B
     g->last = p;
     g->last_ws = workspace;
     g->last_launches = 0;
+    if (g->timing) {
+        if (g->ev.empty()) {
+            cudaEvent_t e;
+            VO2W_CUDA_OK(cudaEventCreate(&e));
+            g->ev.push_back(e);
+        }
+        VO2W_CUDA_OK(cudaEventRecord(g->ev[0], st));
+    }
     if (ws_fresh && g->precision == VO2W_PREC_BF16)   // halo / tail rows of the operand buffers must read as zero
         VO2W_CUDA_OK(cudaMemsetAsync(workspace, 0, p.total, st));
     if (g->precision == VO2W_PREC_BF16) return forward_bf16(g, p, mel, wav, (uint8_t*)workspace, st);
@@ -459,11 +501,12 @@ extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap
     bool found = false;
     const bool bf = g->precision == VO2W_PREC_BF16;
     bool is_bf16_buf = false;
+    float inv_slope = 1.0f;       // "ups.i" in bf16 mode: the value recovered from the stream
     if (name == "conv_pre" && !bf) {
         off = p.c0_f32; C = g->cfg.upsample_initial_channel; L = p.T; found = true;
     }
     for (int i = 0; i < g->n_stage && !found; ++i) {
-        if (name == "ups." + std::to_string(i)) { off = bf ? p.st[i].x : p.st[i].x_f32; found = true; is_bf16_buf = bf; }
+        if (name == "ups." + std::to_string(i)) { off = bf ? p.st[i].xa : p.st[i].x_f32; found = true; is_bf16_buf = bf; inv_slope = bf ? 10.0f : 1.0f; }
         else if (name == "mrf." + std::to_string(i) && !bf) { off = p.st[i].xs; found = true; }
         else if (name == "mrf_act." + std::to_string(i) && bf) { off = p.st[i].mrf; found = true; is_bf16_buf = true; }
         if (found) { C = p.st[i].C; L = p.st[i].L; }
@@ -475,7 +518,7 @@ extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap
     if (is_bf16_buf) {
         float* tmp = nullptr;
         VO2W_CUDA_OK(cudaMalloc(&tmp, n * 4));
-        int rc = unchunk_bf16((const __nv_bfloat16*)(ws + off), tmp, p.B, C, (int)L, (int)vo2w_padded_len(L), 0);
+        int rc = unchunk_bf16((const __nv_bfloat16*)(ws + off), tmp, p.B, C, (int)L, (int)vo2w_padded_len(L), 0, inv_slope);
         if (rc == VO2W_OK && cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = VO2W_E_CUDA;
         cudaFree(tmp);
         if (rc != VO2W_OK) return rc;

@@ -189,7 +189,6 @@ int launch_layers(const PackedLayer* const* layers, const __nv_bfloat16* const* 
     p.div = ep.div;
     p.out_f32 = ep.out_f32;
     p.out_bf16 = ep.out_bf16;
-    p.out_raw = ep.out_raw;
     p.out_slope = ep.out_slope;
     p.out_wave = ep.out_wave;
     p.Cout = L0.Cout;

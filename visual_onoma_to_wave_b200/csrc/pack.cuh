@@ -43,7 +43,6 @@ struct EpilogueSpec {
     float div = 1.0f;
     float* out_f32 = nullptr;
     __nv_bfloat16* out_bf16 = nullptr;
-    __nv_bfloat16* out_raw = nullptr;
     float out_slope = 1.0f;
     float* out_wave = nullptr;
 };

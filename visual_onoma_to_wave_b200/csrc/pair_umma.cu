@@ -314,11 +314,6 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     const uint32_t dst = sm0 + p.xa_off[buf];
                     for (int c = 0; c < chunks; ++c)
                         bulk_g2s(dst + (uint32_t)(c * sg.xa_rows) * 16u, src + (size_t)c * p.Lp * 8, row_bytes, full);
-                    if (t.live) {                        // residual rows of this tile: pull them into L2 for e2
-                        const int orows = min(p.V, p.L - t.l0);
-                        const __nv_bfloat16* rs = sg.x + ((size_t)t.b * chunks * p.Lp + VO2W_PAD_ROWS + t.l0) * 8;
-                        for (int c = 0; c < chunks; ++c) prefetch_l2(rs + (size_t)c * p.Lp * 8, (uint32_t)orows * 16u);
-                    }
                 }
             }
         }
@@ -500,7 +495,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t d2_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D2_EMPTY, 0) : 0u;
         const size_t e_step = (size_t)p.Lp * 8;
-        const __nv_bfloat162 slope2 = __floats2bfloat162_rn(p.out_slope, p.out_slope);
+        const float s_pos = p.scale, s_neg = p.scale * p.out_slope;
         const bool single = n_seg == 1;
         const int back = 2 * p.h2max;
         long long c_wait = 0, c_work = 0;
@@ -524,7 +519,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 for (int s = 0; s < PAIR_MAX_SEG; ++s)
                     if (s < n_seg) {
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].x + e + (size_t)h * e_step));
+                        for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].xa + e + (size_t)h * e_step));
                     }
             };
             if (single) {
@@ -535,7 +530,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     if (ok) {
                         const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].x + e + (size_t)h * e_step));
+                        for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].xa + e + (size_t)h * e_step));
                     }
                 }
             } else {
@@ -556,13 +551,17 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 float v[32];
 #pragma unroll
                 for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]);
+                // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
                 auto add_res = [&](const uint4 (&x)[4]) {
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
-                        const float2 x0 = unpack_bf16x2(x[h].x), x1 = unpack_bf16x2(x[h].y);
-                        const float2 x2 = unpack_bf16x2(x[h].z), x3 = unpack_bf16x2(x[h].w);
-                        v[h * 8 + 0] += x0.x; v[h * 8 + 1] += x0.y; v[h * 8 + 2] += x1.x; v[h * 8 + 3] += x1.y;
-                        v[h * 8 + 4] += x2.x; v[h * 8 + 5] += x2.y; v[h * 8 + 6] += x3.x; v[h * 8 + 7] += x3.y;
+                        const uint32_t w[4] = {x[h].x, x[h].y, x[h].z, x[h].w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 f = unpack_bf16x2(w[i]);
+                            v[h * 8 + 2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[h * 8 + 2 * i] + f.x);
+                            v[h * 8 + 2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[h * 8 + 2 * i + 1] + f.y);
+                        }
                     }
                 };
                 if (ok) {
@@ -577,19 +576,14 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 if (!single && j + 1 < ITEMS) load_item(j + 1);  // next item's residuals fly while this one is stored
                 if (ok) {
                     const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
-                    if (p.scale != 1.0f) {
+                    // out = bf16(leaky_relu(v * scale, out_slope)), one rounding; max(a, a * slope) for slope < 1
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) v[c] *= p.scale;
-                    }
+                    for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
                         uint4 o;
                         o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
                         o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
-                        if (p.out_raw) *(uint4*)(p.out_raw + e + (size_t)h * e_step) = o;
-                        // the activation is taken of the ROUNDED stream value (what a reader of the stream would compute)
-                        o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
-                        o.z = lrelu_bf16x2(o.z, slope2); o.w = lrelu_bf16x2(o.w, slope2);
                         *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
                     }
                 }
@@ -761,11 +755,11 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     const int grid = pair_plan(p, G.seg[0]->C, G.n_seg, ks, dils, cg, B, L, n_sms);
     if (grid < 0) return grid;
     for (int s = 0; s < G.n_seg; ++s) {
-        VO2W_REQUIRE(io.xa[s] && io.x[s], "pair_launch: null input of segment %d", s);
-        p.seg[s].xa = io.xa[s]; p.seg[s].x = io.x[s];
+        VO2W_REQUIRE(io.xa[s], "pair_launch: null input of segment %d", s);
+        p.seg[s].xa = io.xa[s];
         p.seg[s].w1 = G.seg[s]->w1_dev; p.seg[s].w2 = G.seg[s]->w2_dev;
     }
-    p.out_raw = io.out_raw; p.out_act = io.out_act;
+    p.out_act = io.out_act;
     p.out_slope = io.out_slope; p.scale = io.scale;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -810,18 +804,18 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
 
 namespace {
 // bf16 operand buffer [B][C/8][Lp][8] -> fp32 NCL
-__global__ void unchunk_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int C, int L, int Lp) {
+__global__ void unchunk_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int C, int L, int Lp, float inv_slope) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y, b = blockIdx.z;
     if (l >= L) return;
-    out[((size_t)b * C + c) * L + l] =
-        __bfloat162float(x[(((size_t)b * (C >> 3) + (c >> 3)) * Lp + VO2W_PAD_ROWS + l) * 8 + (c & 7)]);
+    const float v = __bfloat162float(x[(((size_t)b * (C >> 3) + (c >> 3)) * Lp + VO2W_PAD_ROWS + l) * 8 + (c & 7)]);
+    out[((size_t)b * C + c) * L + l] = v < 0.f ? v * inv_slope : v;
 }
 }  // namespace
 
-int unchunk_bf16(const __nv_bfloat16* x, float* out, int B, int C, int L, int Lp, cudaStream_t st) {
+int unchunk_bf16(const __nv_bfloat16* x, float* out, int B, int C, int L, int Lp, cudaStream_t st, float inv_slope) {
     dim3 grid((unsigned)vo2w_ceil_div(L, 128), (unsigned)C, (unsigned)B);
-    unchunk_bf16_kernel<<<grid, 128, 0, st>>>(x, out, C, L, Lp);
+    unchunk_bf16_kernel<<<grid, 128, 0, st>>>(x, out, C, L, Lp, inv_slope);
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
 }
@@ -845,8 +839,8 @@ extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const flo
     if (rc == VO2W_OK) rc = make_group(G, pp, n_seg);
     const long long Lp = vo2w_padded_len(L);
     const size_t bytes = (size_t)B * C * Lp * 2;
-    __nv_bfloat16* buf[2 * PAIR_MAX_SEG + 2] = {};   // xa_s, x_s per segment, out_raw, out_act
-    const int n_buf = 2 * n_seg + 2;
+    __nv_bfloat16* buf[PAIR_MAX_SEG + 1] = {};   // the stream of every segment, out_act
+    const int n_buf = n_seg + 1;
     for (int i = 0; i < n_buf && rc == VO2W_OK; ++i) {
         if (cudaMalloc(&buf[i], bytes) != cudaSuccess || cudaMemsetAsync(buf[i], 0, bytes, st) != cudaSuccess) {
             vo2w_set_error("debug_pair: allocation failed");
@@ -855,20 +849,18 @@ extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const flo
     }
     PairIO io;
     for (int s = 0; s < n_seg && rc == VO2W_OK; ++s) {
-        rc = pack_ncl_to_operand(x_dev[s], buf[2 * s], B, C, L, (int)Lp, 0.1f, st);
-        if (rc == VO2W_OK) rc = pack_ncl_to_operand(x_dev[s], buf[2 * s + 1], B, C, L, (int)Lp, 1.0f, st);
-        io.xa[s] = buf[2 * s];
-        io.x[s] = buf[2 * s + 1];
+        rc = pack_ncl_to_operand(x_dev[s], buf[s], B, C, L, (int)Lp, 0.1f, st);
+        io.xa[s] = buf[s];
     }
     if (rc == VO2W_OK) {
-        io.out_raw = out_dev ? buf[2 * n_seg] : nullptr;
-        io.out_act = buf[2 * n_seg + 1];
+        io.out_act = buf[n_seg];
         io.scale = scale;
         io.out_slope = out_slope;
         rc = pair_launch(G, io, B, L, st);
     }
-    if (rc == VO2W_OK && out_dev) rc = unchunk_bf16(buf[2 * n_seg], out_dev, B, C, L, (int)Lp, st);
-    if (rc == VO2W_OK) rc = unchunk_bf16(buf[2 * n_seg + 1], act_dev, B, C, L, (int)Lp, st);
+    // out = the value a consumer recovers from the stream (activation undone), act = the stream itself
+    if (rc == VO2W_OK && out_dev) rc = unchunk_bf16(buf[n_seg], out_dev, B, C, L, (int)Lp, st, 1.0f / out_slope);
+    if (rc == VO2W_OK) rc = unchunk_bf16(buf[n_seg], act_dev, B, C, L, (int)Lp, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (rc == VO2W_OK && e != cudaSuccess) {
         vo2w_set_error("debug_pair: kernel failed: %s", cudaGetErrorString(e));

@@ -1,5 +1,5 @@
 // Fused ResBlock iterations on tcgen05 (sm_100a).  One launch computes, per 128*NB-row tile,
-//     y = sum over segments s of [ x_s + conv2_s(lrelu(conv1_s(lrelu(x_s)) + b1_s)) + b2_s ]
+//     y = sum over segments s of [ x_s + conv2_s(lrelu(conv1_s(lrelu(x_s)) + b1_s)) + b2_s ],  out = bf16(lrelu(scale * y))
 // (scripts/hifigan/models.py:96-103 for one segment; with the last iteration of all ResBlocks of a stage as
 // segments it is also the MRF sum xs of models.py:154-160).  See pair_umma.cu and DESIGN.md.
 #pragma once
@@ -24,8 +24,8 @@
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
 
 struct PairSegP {
-    const __nv_bfloat16* xa;      // conv1 operand = leaky_relu(x, 0.1) as bf16, [B][C/8][Lp][8], zero pad rows
-    const __nv_bfloat16* x;       // residual stream x as raw bf16, same layout
+    const __nv_bfloat16* xa;      // the stream: bf16(leaky_relu(x, 0.1)), [B][C/8][Lp][8], zero pad rows = conv1 operand;
+                                  // the residual x is recovered from it (x = s >= 0 ? s : 10 s)
     const uint8_t* w1;            // packed conv1: [cta rank][item][KB/8][C/CG][8] bf16, item 0 = bias, item 1 + kb*k + tap = weights
     const uint8_t* w2;
     int32_t k, dil;               // conv1: k taps, dilation dil; conv2: k taps, dilation 1
@@ -39,8 +39,7 @@ struct PairSegP {
 struct PairP {
     PairSegP seg[PAIR_MAX_SEG];
     int32_t n_seg;
-    __nv_bfloat16* out_raw;       // optional: y * scale as bf16 (the stream for the next iteration)
-    __nv_bfloat16* out_act;       // leaky_relu(bf16(y * scale), out_slope) as bf16 (operand of the next layer)
+    __nv_bfloat16* out_act;       // bf16(leaky_relu(y * scale, out_slope)): the stream / operand of the next layer
     int32_t C, L, Lp;
     int32_t h2max;
     int32_t NB;                   // 128-row accumulator blocks per CTA tile
@@ -71,8 +70,6 @@ struct PackedGroup {
 
 struct PairIO {
     const __nv_bfloat16* xa[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
-    const __nv_bfloat16* x[PAIR_MAX_SEG] = {nullptr, nullptr, nullptr};
-    __nv_bfloat16* out_raw = nullptr;
     __nv_bfloat16* out_act = nullptr;
     float out_slope = 0.1f;
     float scale = 1.0f;

@@ -219,6 +219,23 @@ class Generator(nn.Module):
         _lib.check(int(n), "vo2w_generator_debug_tap")
         return buf[:n].clone()
 
+    def launch_times(self, x: torch.Tensor):
+        """One forward with a CUDA event around every launch: ([ms per launch], [kind per launch]), kind 0 = layout
+        helper, 1 = single convolution, 2 = fused ResBlock iterations (bench.py's roofline measurement)."""
+        import ctypes as C
+        lib = _lib.lib()
+        handle = self._get_handle(x.device)
+        _lib.check(lib.vo2w_generator_set_timing(handle, 1), "vo2w_generator_set_timing")
+        try:
+            self.forward(x)
+            ms = (C.c_float * 256)()
+            kind = (C.c_int32 * 256)()
+            n = lib.vo2w_generator_get_timing(handle, ms, kind, 256)
+            _lib.check(n, "vo2w_generator_get_timing")
+        finally:
+            lib.vo2w_generator_set_timing(handle, 0)
+        return list(ms[:n]), list(kind[:n])
+
     def refresh(self):
         """Re-pack the weights on the next forward (call after editing parameters in place)."""
         self._drop_handle()

@@ -25,6 +25,8 @@ V1_CONFIG = {  # scripts/hifigan/config.json:11-15,21,24
 }
 
 FLOP_PER_FRAME = 614_105_088
+# the 72 ResBlock convolutions alone (2 x (66 060 288 + 132 120 576 + 66 060 288 + 33 030 144) MAC)
+PAIR_FLOP_PER_FRAME = 594_542_592
 
 
 def layer_shapes(cfg=V1_CONFIG):
