@@ -48,7 +48,9 @@ __device__ __forceinline__ void commit(uint32_t bar) {
 
 // CG cta_group, M/N instruction shape, TS: A from TMEM, TF32, NACC independent accumulators (round-robin),
 // SHIFT: row shift of every second A descriptor (conv taps on a SWIZZLE_NONE K-major tile)
-template <int CG, int M, int N, bool TS, bool TF32, int NACC, int SHIFT>
+// AROWS > 0: the fused kernel's operand pattern -- A tile of AROWS rows per 16-byte channel chunk (LBO = AROWS * 16 B),
+// NACC row blocks of 128 rows, 8 / NACC K=16 steps each, a tap shift of (batch % 3) rows
+template <int CG, int M, int N, bool TS, bool TF32, int NACC, int SHIFT, int AROWS = 0>
 __global__ void __launch_bounds__(128) bench_kernel(const BenchP p, unsigned long long* cycles) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[4];
@@ -80,9 +82,9 @@ __global__ void __launch_bounds__(128) bench_kernel(const BenchP p, unsigned lon
     const uint32_t tmem_base = tmem_base_s;
 
     constexpr int m_cta = M / CG, n_cta = N / CG;
-    constexpr uint32_t a_lbo = (uint32_t)(m_cta + 32) * 16u, b_lbo = (uint32_t)n_cta * 16u;
-    const uint32_t a_smem = smem_u32(smem);                 // 32 KB
-    const uint32_t b_smem = a_smem + 32 * 1024;             // 64 KB
+    constexpr uint32_t a_lbo = AROWS ? (uint32_t)AROWS * 16u : (uint32_t)(m_cta + 32) * 16u, b_lbo = (uint32_t)n_cta * 16u;
+    const uint32_t a_smem = smem_u32(smem);                 // 32 KB (64 KB with AROWS)
+    const uint32_t b_smem = a_smem + (AROWS ? 64 : 32) * 1024;
     if (warp == 1 && cta_rank == 0) {
         constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24) |
                                    (TF32 ? ((2u << 7) | (2u << 10)) : ((1u << 7) | (1u << 10)));
@@ -95,7 +97,13 @@ __global__ void __launch_bounds__(128) bench_kernel(const BenchP p, unsigned lon
                 for (int ks = 0; ks < 8; ++ks) {
                     const uint32_t d = tmem_base + (uint32_t)((ks % NACC) * N);
                     const uint64_t bd = b0 + (uint64_t)(((uint32_t)ks * 2u * b_lbo) >> 4);
-                    if (TS) {
+                    if (AROWS) {
+                        constexpr int KSTEPS = 8 / NACC;
+                        const int blk = ks / KSTEPS, st = ks % KSTEPS;
+                        const uint64_t ad = a0 + (uint64_t)(((uint32_t)blk * 128u * 16u + (uint32_t)st * 2u * a_lbo + (uint32_t)(b % 3) * 16u) >> 4);
+                        const uint64_t bd2 = b0 + (uint64_t)(((uint32_t)st * 2u * b_lbo) >> 4);
+                        mma_ss<CG, TF32>(tmem_base + (uint32_t)(blk * N), ad, bd2, idesc);
+                    } else if (TS) {
                         mma_ts<CG>(d, tmem_base + 448u + (uint32_t)ks * 8u, bd, idesc);
                     } else {
                         const uint64_t ad = a0 + (uint64_t)((((uint32_t)(ks & 3) * 2u * a_lbo) + ((ks & 1) ? SHIFT * 16u : 0u)) >> 4);
@@ -122,10 +130,10 @@ __global__ void __launch_bounds__(128) bench_kernel(const BenchP p, unsigned lon
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
 
-template <int CG, int M, int N, bool TS, bool TF32, int NACC, int SHIFT>
+template <int CG, int M, int N, bool TS, bool TF32, int NACC, int SHIFT, int AROWS = 0>
 static void run(const char* name, int batches, int n_sm) {
     BenchP p{batches};
-    auto kern = bench_kernel<CG, M, N, TS, TF32, NACC, SHIFT>;
+    auto kern = bench_kernel<CG, M, N, TS, TF32, NACC, SHIFT, AROWS>;
     unsigned long long* d_cyc;
     const int n_units = n_sm / CG;
     CK(cudaMalloc(&d_cyc, sizeof(unsigned long long) * n_units));
@@ -176,6 +184,17 @@ int main(int argc, char** argv) {
     const int n_sm = prop.multiProcessorCount;
     printf("device %s, %d SMs, cc %d.%d\n", prop.name, n_sm, prop.major, prop.minor);
     const int bt = argc > 1 ? atoi(argv[1]) : 2048;
+    if (argc > 2) {   // the fused kernel's operand patterns only
+        run<2, 256, 32, false, false, 1, 0>("2CTA SS", bt, n_sm);
+        run<2, 256, 32, false, false, 4, 0>("2CTA SS 4acc", bt, n_sm);
+        run<2, 256, 32, false, false, 4, 0, 514>("pair C32 conv1", bt, n_sm);
+        run<2, 256, 32, false, false, 4, 0, 512>("pair C32 conv2", bt, n_sm);
+        run<2, 256, 32, false, false, 4, 0, 160>("C32 lbo160", bt, n_sm);
+        run<2, 256, 64, false, false, 2, 0, 258>("pair C64 conv1", bt, n_sm);
+        run<2, 256, 64, false, false, 2, 0, 256>("pair C64 conv2", bt, n_sm);
+        run<2, 256, 128, false, false, 2, 0, 258>("pair C128 conv1", bt, n_sm);
+        return 0;
+    }
     run<1, 128, 32, false, false, 1, 0>("SS", bt, n_sm);
     run<1, 128, 64, false, false, 1, 0>("SS", bt, n_sm);
     run<1, 128, 128, false, false, 1, 0>("SS", bt, n_sm);

@@ -145,11 +145,13 @@ enum {
     BAR_W_FULL = 6,                                   // [PAIR_MAX_SLOTS]
     BAR_W_EMPTY = BAR_W_FULL + PAIR_MAX_SLOTS,
     BAR_W_FULL_PEER = BAR_W_EMPTY + PAIR_MAX_SLOTS,   // leader only
-    BAR_D1_FULL = BAR_W_FULL_PEER + PAIR_MAX_SLOTS,   // conv1 accumulators complete
-    BAR_T_FULL,                                       // [4] leader only: 64-channel block kb of the conv2 operand written
-    BAR_D2_FULL = BAR_T_FULL + 4,                     //     by every e1 warp of the pair
-    BAR_D2_EMPTY,                                     // leader only: every e2 warp of the pair has read D2
-    BAR_COUNT
+    // the accumulators and the conv2 operand buffer exist ND times (ND = 2 where TMEM has the room, C <= 64):
+    // the barriers below are indexed by the buffer, unit n uses buffer n % ND with phase (n / ND) & 1
+    BAR_D1_FULL = BAR_W_FULL_PEER + PAIR_MAX_SLOTS,   // [2] conv1 accumulators complete
+    BAR_T_FULL = BAR_D1_FULL + 2,                     // [2][4] leader only: 64-channel block kb of the conv2 operand
+    BAR_D2_FULL = BAR_T_FULL + 8,                     //        written by every e1 warp of the pair
+    BAR_D2_EMPTY = BAR_D2_FULL + 2,                   // [2] leader only: every e2 warp of the pair has read D2
+    BAR_COUNT = BAR_D2_EMPTY + 2
 };
 
 struct TileCoord {
@@ -165,6 +167,14 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     t.b = g / p.tiles_per_utt;
     t.l0 = (g - t.b * p.tiles_per_utt) * p.V;
     return t;
+}
+
+// VO2W_PAIR_PROF=1: event trace of CTA 0 (the leader of pair 0): trace[role][unit][2] timestamps (clock64)
+#define PAIR_TR_UNITS 48
+#define PAIR_TR_ROLES 8     // 0 input producer, 1 conv1 issue, 2 conv2 issue, 3 e1, 4 e2, 5 weight producer
+__device__ __forceinline__ void trace(const PairP& p, int role, int unit, int slot) {
+    if (p.prof && blockIdx.x == 0 && unit < PAIR_TR_UNITS && (threadIdx.x & 31) == 0)
+        p.prof[(size_t)gridDim.x * 16 + ((size_t)role * PAIR_TR_UNITS + unit) * 2 + slot] = (unsigned long long)clock64();
 }
 
 // MMA with both shared-memory descriptors given as their low words (start address and LBO; the high word
@@ -189,28 +199,34 @@ __device__ __forceinline__ void mma_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t 
 // keep:   accumulate on top of what the accumulators hold (conv2 of segments after the first).
 // The whole warp walks the (warp-uniform) loops so that addresses stay in uniform registers; one elected
 // lane issues.  NI issuer warps split the row blocks (issue, not execution, limits the small-N stages).  All descriptor arithmetic is in 16-byte units on the low descriptor word.
-template <int CG, int NB, int KS, int NI>
-__device__ __forceinline__ void issue_conv(const PairP& p, int issuer, uint32_t bar0, uint32_t a_addr, uint32_t a_rows, int n_items,
-                                           int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
+template <int CG, int C, int NB, int KS, int NI>
+__device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int issuer, uint32_t bar0, uint32_t a_addr, uint32_t a_rows,
+                                           int n_items, int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
                                            uint32_t idesc, uint32_t ones_lo, uint32_t& wit, long long& w_wait,
-                                           int k_taps, uint32_t t_parity, long long& t_wait) {
-    const uint32_t n_loc = (uint32_t)p.C / CG;
+                                           int k_taps, uint32_t t_bar, uint32_t t_parity, long long& t_wait, int tr_unit = -1) {
+    constexpr uint32_t n_loc = (uint32_t)C / CG;
+    constexpr uint32_t KB = C < 64 ? C : 64;
+    constexpr uint32_t item_units = n_loc * KB * 2u / 16u;                    // 16-byte units of one weight item
     const uint32_t a_base = ((a_addr >> 4) & 0x3FFFu) | (a_rows << 16);      // LBO = a_rows * 16 B
-    const uint32_t b_lbo_field = n_loc << 16;                                 // LBO = n_loc * 16 B
+    constexpr uint32_t b_lbo_field = n_loc << 16;                             // LBO = n_loc * 16 B
     uint32_t tap = 0, kb = 0;                                                 // items 1.. run kb-major: (kb, tap)
-    const uint32_t kb_rows = ((uint32_t)p.KB >> 3) * a_rows;                  // 16-byte units per 64-channel block
+    const uint32_t kb_rows = (KB >> 3) * a_rows;                              // 16-byte units per 64-channel block
     const uint32_t blk_back = second ? 2u * (uint32_t)p.h2max : 0u;
-    const uint32_t item_units = p.item_bytes >> 4;
+    const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_shift = (uint32_t)p.slots_log2;
+    const int per_stage = p.items_per_stage;
+    const bool no_mma = (p.dbg & 4) != 0;
     int item = 0;
     while (item < n_items) {
-        const uint32_t slot = wit % (uint32_t)p.n_slots, par = (wit / (uint32_t)p.n_slots) & 1u;
-        const long long tw = clock64();
+        const uint32_t slot = wit & slot_mask, par = (wit >> slot_shift) & 1u;
+        long long tw = 0;
+        if (prof) tw = clock64();
         mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
         if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL_PEER + slot), par);
-        w_wait += clock64() - tw;
+        if (prof) w_wait += clock64() - tw;
         __syncwarp();
         tc_fence_after();
-        const int cnt = min(p.items_per_stage, n_items - item);
+        if (prof && tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0);
+        const int cnt = min(per_stage, n_items - item);
         const uint32_t stage_lo = (((ring_addr + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
         for (int i = 0; i < cnt; ++i) {
             const int idx = item + i;
@@ -220,7 +236,7 @@ __device__ __forceinline__ void issue_conv(const PairP& p, int issuer, uint32_t 
                 if (elect_one()) {
 #pragma unroll
                     for (int bi = 0; bi < NB / NI; ++bi)
-                        mma_lo<CG>(d_tmem + (uint32_t)((issuer + bi * NI) * p.C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
+                        mma_lo<CG>(d_tmem + (uint32_t)((issuer + bi * NI) * C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
                 }
                 __syncwarp();
                 continue;
@@ -228,29 +244,32 @@ __device__ __forceinline__ void issue_conv(const PairP& p, int issuer, uint32_t 
             if (second && tap == 0) {
                 // conv2 reads channel block kb of the operand buffer: wait until e1 has written it (the later
                 // blocks are still being converted while these MMAs run)
-                const long long tt = clock64();
-                mbar_wait_cluster(bar0 + 8u * (BAR_T_FULL + kb), t_parity);
-                t_wait += clock64() - tt;
+                long long tt = 0;
+                if (prof) tt = clock64();
+                mbar_wait_cluster(t_bar + 8u * kb, t_parity);
+                if (prof) t_wait += clock64() - tt;
                 __syncwarp();
                 tc_fence_after();
             }
             const uint32_t a_lo = a_base + kb * kb_rows + tap * (uint32_t)dil;
-            if (elect_one()) {
+            if (!no_mma && elect_one()) {
 #pragma unroll
                 for (int bi = 0; bi < NB / NI; ++bi) {
                     const int blk = issuer + bi * NI;                       // this issuer's row blocks
                     const uint32_t a_blk = a_lo + (uint32_t)(blk * 128) - (blk > 0 ? blk_back : 0u);
 #pragma unroll
                     for (int s = 0; s < KS; ++s)
-                        mma_lo<CG>(d_tmem + (uint32_t)(blk * p.C), a_blk + (uint32_t)s * 2u * a_rows,
+                        mma_lo<CG>(d_tmem + (uint32_t)(blk * C), a_blk + (uint32_t)s * 2u * a_rows,
                                    b_lo + (uint32_t)s * 2u * n_loc, idesc, 1u);
                 }
             }
             __syncwarp();
             if (++tap == (uint32_t)k_taps) { tap = 0; ++kb; }
         }
+        if (prof && tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 1);
         if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
         __syncwarp();
+        if (prof && tr_unit >= 0 && item == 0) trace(p, 7, tr_unit, 0);
         item += cnt;
         ++wit;
     }
@@ -262,7 +281,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
     constexpr int KS = C < 64 ? 2 : 4;                       // K=16 steps per weight item (64 input channels, 32 for C=32)
     constexpr int GROUPS = C / 32;                           // 32 accumulator columns per tcgen05.ld
     constexpr int CHUNKS = C / 8;
-    constexpr int NI = NB >= 2 ? 2 : 1;                      // MMA issuer warps
+    constexpr int NI = NB >= 2 ? 2 : 1;                      // MMA issuer warps (they split the row blocks)
+    constexpr int ND = PAIR_ND(C);                           // copies of D1 / D2 / conv2 operand buffer (skewed schedule if 2)
+    static_assert(2 * ND * NB * C <= 512, "accumulators exceed TMEM");
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[BAR_COUNT];
     __shared__ uint32_t tmem_base_s;
@@ -272,14 +293,15 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
     const uint32_t sm0 = smem_u32(smem);
     const uint32_t bar0 = smem_u32(bars);
     const int n_seg = p.n_seg;
+    const int n_units = p.iters * n_seg;             // (tile, segment) units this CTA walks
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < BAR_COUNT; ++i)
             {
             const bool by_issuers = (i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 2) || (i >= BAR_W_EMPTY && i < BAR_W_EMPTY + PAIR_MAX_SLOTS) ||
-                                    i == BAR_D1_FULL || i == BAR_D2_FULL;     // one tcgen05.commit per issuer warp
-            mbar_init(bar0 + 8u * i, (i >= BAR_T_FULL && i < BAR_T_FULL + 4) ? CG * PAIR_E1_WARPS
-                                     : (i == BAR_D2_EMPTY ? CG * PAIR_E2_WARPS : (by_issuers ? NI : 1)));
+                                    (i >= BAR_D1_FULL && i < BAR_D1_FULL + 2) || (i >= BAR_D2_FULL && i < BAR_D2_FULL + 2);   // one tcgen05.commit per issuer warp
+            mbar_init(bar0 + 8u * i, (i >= BAR_T_FULL && i < BAR_T_FULL + 8) ? CG * PAIR_E1_WARPS
+                                     : ((i >= BAR_D2_EMPTY && i < BAR_D2_EMPTY + 2) ? CG * PAIR_E2_WARPS : (by_issuers ? NI : 1)));
         }
         fence_mbar_init();
     }
@@ -298,13 +320,31 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // ================= input tile producer =================
         if (lane == 0) {
             constexpr int chunks = CHUNKS;
+            // The smem tile of unit n + 2 can only be requested once conv1 of unit n has retired, which leaves one
+            // DRAM round trip per two units on the critical path.  So the rows of unit n + pf are pulled into L2
+            // (no shared memory needed) well ahead, and the bulk copy into shared memory is an L2 hit.
+            auto prefetch_unit = [&](int m) {
+                if (m >= n_units) return;
+                const int it = m / n_seg, s = m - it * n_seg;
+                const TileCoord t = tile_of(p, it);
+                if (!t.live) return;
+                const PairSegP& sg = p.seg[s];
+                const int start = VO2W_PAD_ROWS + t.l0 - sg.h2 - sg.h1;
+                const int rows = min(sg.xa_rows, p.Lp - start);
+                const __nv_bfloat16* src = sg.xa + ((size_t)t.b * chunks * p.Lp + start) * 8;
+                for (int c = 0; c < chunks; ++c) prefetch_l2(src + (size_t)c * p.Lp * 8, (uint32_t)rows * 16u);
+            };
+            for (int m = 2; m < 2 + p.pf; ++m) prefetch_unit(m);
             int n = 0;                                   // running (tile, segment) counter -> buffer and phase
             for (int it = 0; it < p.iters; ++it) {
                 const TileCoord t = tile_of(p, it);
                 for (int s = 0; s < n_seg; ++s, ++n) {
                     const PairSegP& sg = p.seg[s];
-                    const int buf = n % p.xa_bufs, use = n / p.xa_bufs;
+                    const int buf = n & (p.xa_bufs - 1), use = n >> (p.xa_bufs - 1);
+                    if (p.pf) prefetch_unit(n + 2 + p.pf);
+                    trace(p, 0, n, 0);
                     if (use > 0) mbar_wait(bar0 + 8u * (BAR_XA_EMPTY + buf), (uint32_t)((use - 1) & 1));
+                    trace(p, 0, n, 1);
                     const int start = VO2W_PAD_ROWS + t.l0 - sg.h2 - sg.h1;   // first staged row inside the padded axis
                     const int rows = min(sg.xa_rows, p.Lp - start);
                     const uint32_t row_bytes = (uint32_t)rows * 16u;
@@ -318,95 +358,149 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             }
         }
     } else if (warp == PAIR_WARP_W) {
-        // ================= weight producer =================
+        // ================= weight producer (same conv order as the MMA issuers) =================
         if (lane == 0) {
             uint32_t wit = 0;
-            for (int it = 0; it < p.iters; ++it) {
-                for (int s = 0; s < n_seg; ++s) {
-                    const PairSegP& sg = p.seg[s];
-                    for (int conv = 0; conv < 2; ++conv) {
-                        const uint8_t* base = (conv ? sg.w2 : sg.w1) + (size_t)rank * sg.conv_bytes_rank;
-                        for (int item = 0; item < sg.n_items; item += p.items_per_stage, ++wit) {
-                            const int cnt = min(p.items_per_stage, sg.n_items - item);
-                            const uint32_t slot = wit % (uint32_t)p.n_slots, use = wit / (uint32_t)p.n_slots;
-                            if (use > 0) mbar_wait(bar0 + 8u * (BAR_W_EMPTY + slot), (use - 1) & 1u);
-                            const uint32_t bytes = (uint32_t)cnt * p.item_bytes;
-                            const uint32_t full = bar0 + 8u * (BAR_W_FULL + slot);
-                            mbar_arrive_expect_tx(full, bytes);
-                            bulk_g2s(sm0 + p.ring_off + slot * p.stage_bytes, base + (size_t)item * p.item_bytes, bytes, full);
-                        }
-                    }
+            const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_shift = (uint32_t)p.slots_log2;
+            auto feed = [&](int n, int s, int conv) {
+                const PairSegP& sg = p.seg[s];
+                const uint8_t* base = (conv ? sg.w2 : sg.w1) + (size_t)rank * sg.conv_bytes_rank;
+                trace(p, 5, n, conv);
+                for (int item = 0; item < sg.n_items; item += p.items_per_stage, ++wit) {
+                    const int cnt = min(p.items_per_stage, sg.n_items - item);
+                    const uint32_t slot = wit & slot_mask, use = wit >> slot_shift;
+                    if (use > 0) mbar_wait(bar0 + 8u * (BAR_W_EMPTY + slot), (use - 1) & 1u);
+                    const uint32_t bytes = (uint32_t)cnt * p.item_bytes;
+                    const uint32_t full = bar0 + 8u * (BAR_W_FULL + slot);
+                    mbar_arrive_expect_tx(full, bytes);
+                    bulk_g2s(sm0 + p.ring_off + slot * p.stage_bytes, base + (size_t)item * p.item_bytes, bytes, full);
+                }
+            };
+            int s2 = 0;
+            if (ND == 2) {
+                int s1 = 0;
+                feed(0, 0, 0);
+                for (int n = 0; n < n_units; ++n) {
+                    if (++s1 == n_seg) s1 = 0;
+                    if (n + 1 < n_units) feed(n + 1, s1, 0);
+                    feed(n, s2, 1);
+                    if (++s2 == n_seg) s2 = 0;
+                }
+            } else {
+                for (int n = 0; n < n_units; ++n) {
+                    feed(n, s2, 0); feed(n, s2, 1);
+                    if (++s2 == n_seg) s2 = 0;
                 }
             }
         }
     } else if (warp >= PAIR_WARP_MMA0 && warp < PAIR_WARP_MMA0 + NI && rank == 0) {
-        {
-            const int issuer = warp - PAIR_WARP_MMA0;
-            // ================= MMA issuer (whole warp loops, one elected lane issues) =================
-            const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
-            const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
-            const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(NB * C);
-            uint32_t wit = 0;
-            int n = 0;
-            long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0, c_drain = 0;
-            const long long c_start = clock64();
-            for (int it = 0; it < p.iters; ++it) {
-                for (int s = 0; s < n_seg; ++s, ++n) {
-                    const PairSegP& sg = p.seg[s];
-                    const int buf = n % p.xa_bufs, use = n / p.xa_bufs;
-                    long long c0 = clock64();
-                    mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
-                    if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
-                    c_xa += clock64() - c0;
-                    tc_fence_after();
-                    issue_conv<CG, NB, KS, NI>(p, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false, d1,
-                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, c_t);
-                    if (elect_one()) {
-                        mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));   // input tile reusable
-                        mma_commit<CG>(bar0 + 8u * BAR_D1_FULL);            // e1 may start
-                    }
-                    __syncwarp();
-                    if (p.prof) {   // profiling only: how long the tensor pipe still runs after the last issue
-                        const long long cd = clock64();
-                        mbar_wait(bar0 + 8u * BAR_D1_FULL, (uint32_t)(n & 1));
-                        c_drain += clock64() - cd;
-                    }
-                    // D2 drained by the previous tile's e2 (the operand buffer is awaited per channel block inside)
-                    c0 = clock64();
-                    if (s == 0 && it > 0) mbar_wait_cluster(bar0 + 8u * BAR_D2_EMPTY, (uint32_t)((it - 1) & 1));
-                    c_d2 += clock64() - c0;
-                    tc_fence_after();
-                    issue_conv<CG, NB, KS, NI>(p, issuer, bar0, sm0 + p.t_off, (uint32_t)p.t_rows, sg.n_items, 1, true, s > 0, d2,
-                                   sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, (uint32_t)(n & 1), c_t);
-                    if (s == n_seg - 1) {
-                        if (elect_one()) mma_commit<CG>(bar0 + 8u * BAR_D2_FULL);
-                        __syncwarp();
-                    }
-                }
+        // ================= MMA issuers (whole warp loops, one elected lane issues) =================
+        // The NI issuer warps walk the same schedule in lock step and split the row blocks of every weight item:
+        // a single thread cannot issue the small-N MMAs as fast as the tensor pipe retires them.
+        // ND == 2: skewed schedule  c1(0), { c1(n+1), c2(n) }  -- e1 of unit n runs under conv1 of unit n+1.
+        // In-order execution of one thread's MMAs gives the implicit orderings: conv1(n+ND) is issued after the
+        // T_FULL wait of conv2(n) (D1 free), and e1(n+ND) starts after conv1(n+ND), issued after conv2(n) (t free).
+        const int issuer = warp - PAIR_WARP_MMA0;
+        const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
+        const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
+        const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(ND * NB * C);
+        uint32_t wit = 0;
+        long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0;
+        const bool prof = p.prof != nullptr;
+        const long long c_start = clock64();
+        const int xa_mask = p.xa_bufs - 1, xa_shift = p.xa_bufs - 1;     // xa_bufs is 1 or 2
+        // (n, s): unit and its segment; no divisions on this path
+        auto conv1 = [&](int n, int s) {
+            const PairSegP& sg = p.seg[s];
+            const int buf = n & xa_mask, use = n >> xa_shift;
+            long long c0 = 0;
+            if (prof) c0 = clock64();
+            mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+            if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
+            if (prof) { c_xa += clock64() - c0; if (issuer == 0) trace(p, 1, n, 0); }
+            tc_fence_after();
+            issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
+                           d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, issuer == 0 ? n : -1);
+            if (elect_one()) {
+                mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));        // input tile reusable
+                mma_commit<CG>(bar0 + 8u * (BAR_D1_FULL + n % ND));      // e1 may start
             }
-            if (p.prof && lane == 0 && issuer == 0) {
-                unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
-                o[0] = (unsigned long long)(clock64() - c_start);
-                o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
-                o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2; o[10] = (unsigned long long)c_drain;
+            __syncwarp();
+            if (prof && issuer == 0) trace(p, 1, n, 1);
+        };
+        auto conv2 = [&](int n, int it, int s) {
+            const PairSegP& sg = p.seg[s];
+            // D2[it % ND] drained by the e2 of tile it - ND (the operand buffer is awaited per channel block inside)
+            long long c0 = 0;
+            if (prof) c0 = clock64();
+            if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
+            if (prof) { c_d2 += clock64() - c0; if (issuer == 0) trace(p, 2, n, 0); }
+            tc_fence_after();
+            issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
+                           true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t);
+            if (s == n_seg - 1) {
+                if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
+                __syncwarp();
             }
+            if (prof && issuer == 0) trace(p, 2, n, 1);
+        };
+        int it2 = 0, s2 = 0;                          // (tile, segment) of the unit conv2 works on
+        if (ND == 2) {
+            int s1 = 0;                               // segment of the unit conv1 works on (one unit ahead)
+            conv1(0, 0);
+            for (int n = 0; n < n_units; ++n) {
+                if (++s1 == n_seg) s1 = 0;
+                if (n + 1 < n_units) conv1(n + 1, s1);
+                conv2(n, it2, s2);
+                if (++s2 == n_seg) { s2 = 0; ++it2; }
+            }
+        } else {
+            for (int n = 0; n < n_units; ++n) {
+                conv1(n, s2);
+                conv2(n, it2, s2);
+                if (++s2 == n_seg) { s2 = 0; ++it2; }
+            }
+        }
+        if (p.prof && lane == 0 && issuer == 0) {
+            unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
+            o[0] = (unsigned long long)(clock64() - c_start);
+            o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
+            o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2;
         }
     } else if (warp == PAIR_WARP_MMA0 && rank != 0) {
         if (lane == 0) {
             // ================= peer relay: forward "landed" events to the leader's barriers =================
             uint32_t wit = 0;
-            int n = 0;
-            for (int it = 0; it < p.iters; ++it) {
-                for (int s = 0; s < n_seg; ++s, ++n) {
-                    const int buf = n % p.xa_bufs, use = n / p.xa_bufs;
-                    mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
-                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_XA_FULL_PEER + buf), 0));
-                    const int stages = 2 * ((p.seg[s].n_items + p.items_per_stage - 1) / p.items_per_stage);
-                    for (int q = 0; q < stages; ++q, ++wit) {
-                        const uint32_t slot = wit % (uint32_t)p.n_slots, par = (wit / (uint32_t)p.n_slots) & 1u;
-                        mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
-                        mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_W_FULL_PEER + slot), 0));
-                    }
+            const int xa_mask = p.xa_bufs - 1, xa_shift = p.xa_bufs - 1;
+            const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_shift = (uint32_t)p.slots_log2;
+            auto relay_xa = [&](int n) {
+                const int buf = n & xa_mask, use = n >> xa_shift;
+                mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+                mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_XA_FULL_PEER + buf), 0));
+            };
+            auto relay_w = [&](int s) {       // the ring stages of one convolution of segment s
+                const int stages = p.seg[s].n_stages;
+                for (int q = 0; q < stages; ++q, ++wit) {
+                    const uint32_t slot = wit & slot_mask, par = (wit >> slot_shift) & 1u;
+                    mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
+                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_W_FULL_PEER + slot), 0));
+                }
+            };
+            int s2 = 0;
+            if (ND == 2) {
+                int s1 = 0;
+                relay_xa(0); relay_w(0);
+                for (int n = 0; n < n_units; ++n) {
+                    if (++s1 == n_seg) s1 = 0;
+                    if (n + 1 < n_units) { relay_xa(n + 1); relay_w(s1); }
+                    relay_w(s2);
+                    if (++s2 == n_seg) s2 = 0;
+                }
+            } else {
+                for (int n = 0; n < n_units; ++n) {
+                    relay_xa(n); relay_w(s2); relay_w(s2);
+                    if (++s2 == n_seg) s2 = 0;
                 }
             }
         }
@@ -424,7 +518,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const __nv_bfloat162 slope2 = __floats2bfloat162_rn(0.1f, 0.1f);
         const uint32_t t_row0 = sm0 + p.t_off + (uint32_t)q * 16u;
         // convert 32 accumulator columns of one row block: bf16, leaky-relu, 4 x 16-byte stores
-        auto convert = [&](const uint32_t (&r)[32], int g, int blk, bool inside) {
+        auto convert = [&](const uint32_t (&r)[32], uint32_t t_row, int g, int blk, bool inside) {
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
                 uint4 o;
@@ -435,7 +529,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
                 o.z = lrelu_bf16x2(o.z, slope2); o.w = lrelu_bf16x2(o.w, slope2);
                 if (!inside) o = make_uint4(0u, 0u, 0u, 0u);
-                st_shared_v4(t_row0 + (uint32_t)(((g * 4 + h) * NB * 128 + blk * 128) * 16), o);
+                st_shared_v4(t_row + (uint32_t)(((g * 4 + h) * NB * 128 + blk * 128) * 16), o);
             }
         };
         int n = 0;
@@ -445,35 +539,42 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             for (int s = 0; s < n_seg; ++s, ++n) {
                 const int t0 = t.l0 - p.seg[s].h2 + q;   // sample index of this thread's operand row in block 0
                 const long long c0 = clock64();
-                mbar_wait(bar0 + 8u * BAR_D1_FULL, (uint32_t)(n & 1));
+                const int nd = n % ND;                   // accumulator / operand buffer of this unit
+                mbar_wait(bar0 + 8u * (BAR_D1_FULL + nd), (uint32_t)((n / ND) & 1));
                 const long long c1 = clock64();
                 c_wait += c1 - c0;
+                if (warp == PAIR_E1_WARP0) trace(p, 3, n, 0);
                 tc_fence_after();
+                const uint32_t t_acc = t_lane + (uint32_t)(nd * NB * C);
+                const uint32_t t_row = t_row0 + (uint32_t)nd * p.t_bytes;
 #pragma unroll
                 for (int u = 0; u < UNITS; u += 2) {             // g-major unit order; both loads precede the wait
                     const int g0 = u / NB, b0 = u % NB, g1 = (u + 1) / NB, b1 = (u + 1) % NB;
                     uint32_t ra[32], rb[32];
                     const long long cl0 = clock64();
-                    tmem_ld32(t_lane + (uint32_t)(b0 * C + g0 * 32), ra);
-                    tmem_ld32(t_lane + (uint32_t)(b1 * C + g1 * 32), rb);
+                    tmem_ld32(t_acc + (uint32_t)(b0 * C + g0 * 32), ra);
+                    tmem_ld32(t_acc + (uint32_t)(b1 * C + g1 * 32), rb);
                     tmem_ld_wait();
                     c_ld += clock64() - cl0;
                     const int r0 = t0 + b0 * 128, r1 = t0 + b1 * 128;      // conv2 zero-pads outside the utterance
-                    convert(ra, g0, b0, r0 >= 0 && r0 < p.L);
-                    convert(rb, g1, b1, r1 >= 0 && r1 < p.L);
+                    if (!(p.dbg & 2)) {
+                        convert(ra, t_row, g0, b0, r0 >= 0 && r0 < p.L);
+                        convert(rb, t_row, g1, b1, r1 >= 0 && r1 < p.L);
+                    }
                     if ((u + 2) % UNITS_PER_KB == 0) {
                         // channel block (u + 1) / UNITS_PER_KB of the operand is complete for this warp's rows
                         fence_proxy_async();             // generic-proxy stores -> visible to the tensor core (async proxy)
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) {
-                            const uint32_t bar = t_full_addr + 8u * (uint32_t)((u + 1) / UNITS_PER_KB);
+                            const uint32_t bar = t_full_addr + 8u * (uint32_t)(4 * nd + (u + 1) / UNITS_PER_KB);
                             if (CG == 2) mbar_arrive_remote(bar);
                             else mbar_arrive(bar);
                         }
                     }
                 }
                 const long long c2 = clock64();
+                if (warp == PAIR_E1_WARP0) trace(p, 3, n, 1);
                 c_work += clock64() - c1;
                 c_fence += clock64() - c2;
             }
@@ -493,7 +594,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const int q = q4 * 32 + lane;
         const int half = warp >> 2;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        const uint32_t d2_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D2_EMPTY, 0) : 0u;
+        const uint32_t d2_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D2_EMPTY, 0) : bar0 + 8u * BAR_D2_EMPTY;
         const size_t e_step = (size_t)p.Lp * 8;
         const float s_pos = p.scale, s_neg = p.scale * p.out_slope;
         const bool single = n_seg == 1;
@@ -508,7 +609,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 blk = i / GROUPS;
                 g = i % GROUPS;
                 rel = blk == 0 ? 0 : blk * 128 - back;
-                ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back);
+                ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
             };
             auto load_item = [&](int j) {                // MRF launch: all segments of item j
                 int blk, g, rel; bool ok;
@@ -537,16 +638,18 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 load_item(0);
             }
             const long long c0 = clock64();
-            mbar_wait(bar0 + 8u * BAR_D2_FULL, (uint32_t)(it & 1));
+            const int nd = it % ND;
+            mbar_wait(bar0 + 8u * (BAR_D2_FULL + nd), (uint32_t)((it / ND) & 1));
             const long long c1 = clock64();
             c_wait += c1 - c0;
+            if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 0);
             tc_fence_after();
 #pragma unroll
             for (int j = 0; j < ITEMS; ++j) {
                 int blk, g, rel; bool ok;
                 item_geom(j, blk, g, rel, ok);
                 uint32_t r[32];
-                tmem_ld32(t_lane + (uint32_t)((NB + blk) * C + g * 32), r);
+                tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk) * C + g * 32), r);
                 tmem_ld_wait();
                 float v[32];
 #pragma unroll
@@ -591,10 +694,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (CG == 2) mbar_arrive_remote(d2_empty_addr);
-                else mbar_arrive(bar0 + 8u * BAR_D2_EMPTY);
+                if (CG == 2) mbar_arrive_remote(d2_empty_addr + 8u * (uint32_t)nd);
+                else mbar_arrive(d2_empty_addr + 8u * (uint32_t)nd);
             }
             c_work += clock64() - c1;
+            if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 1);
         }
         if (p.prof && warp == 0 && lane == 0) {
             p.prof[(size_t)blockIdx.x * 16 + 7] = (unsigned long long)c_wait;
@@ -709,15 +813,20 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     if (p.items_per_stage > kmax * kbs + 1) p.items_per_stage = kmax * kbs + 1;
     p.stage_bytes = (uint32_t)p.items_per_stage * p.item_bytes;
     p.n_slots = p.stage_bytes > 16384u ? 2 : PAIR_MAX_SLOTS;
+    p.slots_log2 = p.n_slots == 2 ? 1 : 2;
+    for (int s = 0; s < n_seg; ++s) p.seg[s].n_stages = (p.seg[s].n_items + p.items_per_stage - 1) / p.items_per_stage;
     p.t_rows = 128 * p.NB;
     const uint32_t xa_bytes = (uint32_t)(128 * p.NB + 2 * h1max) * C * 2, t_bytes = (uint32_t)p.t_rows * C * 2;
     const uint32_t ones_bytes = 2u * 128u * 16u;
-    const uint32_t fixed = t_bytes + (uint32_t)p.n_slots * p.stage_bytes + ones_bytes;
+    p.t_bufs = PAIR_ND(C);
+    p.t_bytes = t_bytes;
+    const uint32_t fixed = (uint32_t)p.t_bufs * t_bytes + (uint32_t)p.n_slots * p.stage_bytes + ones_bytes;
     p.xa_bufs = (fixed + 2 * xa_bytes <= PAIR_SMEM_LIMIT) ? 2 : 1;
+    VO2W_REQUIRE(2 * p.t_bufs * p.NB * C <= 512, "pair_plan: accumulators exceed TMEM");
     uint32_t off = 0;
     for (int i = 0; i < p.xa_bufs; ++i) { p.xa_off[i] = off; off += xa_bytes; }
     if (p.xa_bufs == 1) p.xa_off[1] = p.xa_off[0];
-    p.t_off = off; off += t_bytes;
+    p.t_off = off; off += (uint32_t)p.t_bufs * t_bytes;
     p.ring_off = off; off += (uint32_t)p.n_slots * p.stage_bytes;
     p.ones_off = off; off += ones_bytes;
     p.smem_bytes = off;
@@ -772,13 +881,17 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     cfg.attrs = at;
     cfg.numAttrs = 1;
     static const bool prof_on = getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';
+    static const int dbg = getenv("VO2W_PAIR_DBG") ? atoi(getenv("VO2W_PAIR_DBG")) : 0;   // timing experiments only (results are wrong)
+    p.dbg = dbg;
+    static const int pf = getenv("VO2W_PAIR_PF") ? atoi(getenv("VO2W_PAIR_PF")) : 0;
+    p.pf = pf;
     if (prof_on) {
-        VO2W_CUDA_OK(cudaMalloc(&p.prof, (size_t)grid * 16 * 8));
-        VO2W_CUDA_OK(cudaMemsetAsync(p.prof, 0, (size_t)grid * 16 * 8, st));
+        VO2W_CUDA_OK(cudaMalloc(&p.prof, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8));
+        VO2W_CUDA_OK(cudaMemsetAsync(p.prof, 0, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8, st));
     }
     VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C), p));
     if (prof_on) {   // debug aid: per-role cycle accounting, averaged over the CTAs that recorded it
-        std::vector<unsigned long long> h((size_t)grid * 16);
+        std::vector<unsigned long long> h((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2);
         VO2W_CUDA_OK(cudaStreamSynchronize(st));
         VO2W_CUDA_OK(cudaMemcpy(h.data(), p.prof, h.size() * 8, cudaMemcpyDeviceToHost));
         cudaFree(p.prof);
@@ -789,10 +902,25 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
             for (int i = 0; i < 11; ++i) a[i] += (double)h[(size_t)b * 16 + i];
         }
         const double dl = nl ? nl : 1, dg = grid;
-        fprintf(stderr, "[pair prof] C=%d segs=%d k0=%d NB=%d iters=%d tiles=%d | mma total %.0f: wait xa %.0f w %.0f t %.0f d2e %.0f drain1 %.0f | "
+        fprintf(stderr, "[pair prof] C=%d segs=%d k0=%d NB=%d iters=%d tiles=%d | mma total %.0f: wait xa %.0f w %.0f t %.0f d2e %.0f | "
                         "e1 wait %.0f work %.0f (tmem ld+wait %.0f) | e2 wait %.0f work %.0f (cycles per CTA)\n",
-                p.C, p.n_seg, p.seg[0].k, p.NB, p.iters, p.n_tiles, a[0] / dl, a[1] / dl, a[2] / dl, a[3] / dl, a[4] / dl, a[10] / dl,
+                p.C, p.n_seg, p.seg[0].k, p.NB, p.iters, p.n_tiles, a[0] / dl, a[1] / dl, a[2] / dl, a[3] / dl, a[4] / dl,
                 a[5] / dg, a[6] / dg, a[9] / dg, a[7] / dg, a[8] / dg);
+        static const bool trace_on = getenv("VO2W_PAIR_TRACE") && getenv("VO2W_PAIR_TRACE")[0] == '1';
+        if (trace_on) {   // CTA 0, units 16..27: cycles since conv1 of unit 16 was ready to issue
+            const unsigned long long* tr = h.data() + (size_t)grid * 16;
+            auto at = [&](int role, int u, int sl) { return (long long)tr[((size_t)role * PAIR_TR_UNITS + u) * 2 + sl]; };
+            const long long t0 = at(1, 16, 0);
+            static const char* names[PAIR_TR_ROLES] = {"xa producer (idle, EMPTY seen)", "conv1 issue (start, done)", "conv2 issue (start, done)",
+                                                       "e1 (D1 full seen, done)", "e2 (D2 full seen, done)", "w producer (conv1, conv2)",
+                                                       "conv1 (W seen, items issued)", "conv1 (W_EMPTY committed, -)"};
+            for (int role = 0; role < PAIR_TR_ROLES; ++role) {
+                fprintf(stderr, "  [trace] %-32s", names[role]);
+                for (int u = 16; u < 28 && u < p.iters * p.n_seg; ++u)
+                    fprintf(stderr, " u%d:%lld,%lld", u, at(role, u, 0) ? at(role, u, 0) - t0 : -1, at(role, u, 1) ? at(role, u, 1) - t0 : -1);
+                fprintf(stderr, "\n");
+            }
+        }
     }
     return VO2W_OK;
 }

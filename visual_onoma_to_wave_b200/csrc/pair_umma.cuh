@@ -21,6 +21,10 @@
 #define PAIR_WARP_MMA0 14
 #define PAIR_MAX_SLOTS 4
 #define PAIR_MAX_SEG 3
+// Copies of the accumulators D1 / D2 (TMEM) and of the conv2 operand buffer (shared memory).  With 2 the MMA warp
+// runs a skewed schedule -- conv1 of unit n+1 is issued before conv2 of unit n -- so that the conv1 epilogue (e1)
+// of a unit overlaps tensor-core work instead of stalling it.  TMEM (512 columns) has the room for C <= 64.
+#define PAIR_ND(C) ((C) <= 64 ? 2 : 1)
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
 
 struct PairSegP {
@@ -33,7 +37,7 @@ struct PairSegP {
     int32_t n_items;              // 1 + k * (C / KB)
     int32_t xa_rows;              // 128*NB + 2*h1
     uint32_t conv_bytes_rank;     // bytes of one packed conv per CTA rank
-    uint32_t pad_;
+    int32_t n_stages;             // ring stages of one conv = ceil(n_items / items_per_stage)
 };
 
 struct PairP {
@@ -47,11 +51,16 @@ struct PairP {
     int32_t tiles_per_utt, n_tiles, iters;
     float out_slope, scale;
     int32_t t_rows, xa_bufs;
+    int32_t t_bufs;               // = PAIR_ND(C): copies of the conv2 operand buffer (and of D1 / D2 in TMEM)
+    uint32_t t_bytes;             // bytes of one conv2 operand buffer
     int32_t KB, ksteps, kbs_log2; // input channels per item, K=16 steps per item, log2(C / KB)
-    int32_t items_per_stage, n_slots;
+    int32_t items_per_stage, n_slots, slots_log2;   // n_slots is 2 or 4
     uint32_t item_bytes, stage_bytes;
     uint32_t xa_off[2], t_off, ring_off, ones_off;   // byte offsets into dynamic shared memory
     uint32_t smem_bytes;
+    int32_t pf;                   // units (tile x segment) the input rows are prefetched into L2 ahead of their bulk copy
+    int32_t dbg;                  // VO2W_PAIR_DBG bit mask: what-if timing experiments (1: e2 without global traffic,
+                                  // 2: e1 without conversion, 4: no MMAs); results are wrong when set
     unsigned long long* prof;     // optional [grid][16] cycle counters (VO2W_PAIR_PROF=1), else null
 };
 
