@@ -2,4 +2,5 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for d in 0; do TAG=dbg$d VO2W_PAIR_DBG=$d timeout 200 python tools/launch_times.py 64 2>&1 | grep -v Removing; done | tee gpurun_out/exp.log
+TAG=new timeout 200 python tools/launch_times.py 64 2>&1 | grep -v Removing | tee gpurun_out/exp.log
+TAG=b16 timeout 200 python tools/launch_times.py 16 2>&1 | grep -v Removing | tee -a gpurun_out/exp.log

@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int l0 = blockIdx.x * VO2W_TILE_M, ty = blockIdx.y, b = blockIdx.z;
+    const int l0 = blockIdx.x * VO2W_TILE_M * p.n_blk, ty = blockIdx.y, b = blockIdx.z;   // n_blk row blocks of 128 per CTA
 
     const uint32_t a_smem = smem_u32(smem);
     const uint32_t b_smem = a_smem + p.a_bytes;
@@ -57,12 +57,14 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
             for (int s = 0; s < p.n_seg; ++s) {
                 const USeg& sg = p.seg[s];
                 if (s > 0) mbar_wait(a_empty, (uint32_t)((s - 1) & 1));
-                const uint32_t row_bytes = (uint32_t)sg.rows * 16u;
+                const int start = VO2W_PAD_ROWS + l0 - sg.halo_l;         // first staged row inside the padded axis
+                const uint32_t row_bytes = (uint32_t)min(sg.rows, p.Lp_in - start) * 16u;   // the last tile may be short
+                const uint32_t chunk_stride = (uint32_t)sg.rows * 16u;
                 const int chunks = p.Cin >> 3;
                 mbar_arrive_expect_tx(a_full, row_bytes * (uint32_t)chunks);
-                const __nv_bfloat16* src = sg.in + ((size_t)b * chunks * p.Lp_in + (VO2W_PAD_ROWS + l0 - sg.halo_l)) * 8;
+                const __nv_bfloat16* src = sg.in + ((size_t)b * chunks * p.Lp_in + start) * 8;
                 for (int c = 0; c < chunks; ++c)
-                    bulk_g2s(a_smem + (uint32_t)c * row_bytes, src + (size_t)c * p.Lp_in * 8, row_bytes, a_full);
+                    bulk_g2s(a_smem + (uint32_t)c * chunk_stride, src + (size_t)c * p.Lp_in * 8, row_bytes, a_full);
                 const uint8_t* wt = (const uint8_t*)sg.w + (size_t)ty * sg.w_tile_stride;
                 for (int i = 0; i < sg.n_items; ++i) {
                     const uint32_t bytes = (uint32_t)sg.items[i].n_size * (uint32_t)KB * 2u;
@@ -103,14 +105,16 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
                         tc_fence_after();
                         if (elect_one_sync()) {
                             const uint32_t bs = b_smem + (uint32_t)stage * p.stage_bytes;
-                            for (int st = 0; st < p.kb_steps; ++st) {
-                                const uint32_t kstep = (uint32_t)(kb * p.kb_steps + st);
-                                const uint32_t a_addr = a_smem + (kstep * 2u * (uint32_t)sg.rows + (uint32_t)item.row_shift + extra_shift) * 16u;
-                                const uint32_t b_addr = bs + (uint32_t)st * 2u * b_lbo;
-                                const uint32_t accumulate = (item.zero_init && kb == 0 && st == 0) ? 0u : 1u;
-                                umma_bf16(d_tmem, umma_smem_desc(a_addr, a_lbo, 128u), umma_smem_desc(b_addr, b_lbo, 128u),
-                                          idesc, accumulate);
-                            }
+                            for (int blk = 0; blk < p.n_blk; ++blk)      // every weight stage serves all row blocks
+                                for (int st = 0; st < p.kb_steps; ++st) {
+                                    const uint32_t kstep = (uint32_t)(kb * p.kb_steps + st);
+                                    const uint32_t a_addr = a_smem + (kstep * 2u * (uint32_t)sg.rows + (uint32_t)(blk * VO2W_TILE_M) +
+                                                                      (uint32_t)item.row_shift + extra_shift) * 16u;
+                                    const uint32_t b_addr = bs + (uint32_t)st * 2u * b_lbo;
+                                    const uint32_t accumulate = (item.zero_init && kb == 0 && st == 0) ? 0u : 1u;
+                                    umma_bf16(d_tmem + (uint32_t)(blk * p.n_cols), umma_smem_desc(a_addr, a_lbo, 128u),
+                                              umma_smem_desc(b_addr, b_lbo, 128u), idesc, accumulate);
+                                }
                             umma_commit(empty_bar(stage));   // stage reusable once these MMAs retire
                         }
                         __syncwarp();
@@ -125,21 +129,13 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
     } else {
         // ===================== epilogue: TMEM -> registers -> global =====================
         const int quarter = warp & 3;                    // TMEM lanes this warp may read
-        const int q = quarter * 32 + lane;               // row inside the tile
-        const int row = l0 + q;
-        const bool valid = row < p.M_valid;
+        const int q = quarter * 32 + lane;               // row inside a 128-row block
         mbar_wait(acc_full, 0);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const float* bias = p.bias + (size_t)ty * p.n_cols;
-        const int groups = p.n_cols >> 3;
-        for (int g = 0; g < groups; ++g) {
-            uint32_t r[8];
-            __syncwarp();                                // tcgen05.ld is warp-collective (.sync.aligned)
-            tmem_ld8(t_row + (uint32_t)(g * 8), r);
-            tmem_ld_wait();
-            if (valid) {
-            const int n = g * 8;
+        // 8 accumulator columns [n, n + 8) of output row `row`: bias, residuals, activation, store
+        auto emit8 = [&](const uint32_t (&r)[8], int n, int row) {
             int co, lo;
             if (p.up_s == 1) {
                 co = ty * p.n_cols + n;
@@ -156,8 +152,9 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
             v[4] = __uint_as_float(r[4]) + b1.x; v[5] = __uint_as_float(r[5]) + b1.y;
             v[6] = __uint_as_float(r[6]) + b1.z; v[7] = __uint_as_float(r[7]) + b1.w;
             if (p.out_wave) {
-                if (g == 0) p.out_wave[(size_t)b * p.L_out + lo] = tanhf(v[0]);
-            } else {
+                if (n == 0) p.out_wave[(size_t)b * p.L_out + lo] = tanhf(v[0]);
+                return;
+            }
             const size_t f_off = (((size_t)b * (p.Cout >> 2) + (co >> 2)) * p.L_out + lo) * 4;   // chunk co/4
             const size_t f_step = (size_t)p.L_out * 4;                                           // chunk co/4 + 1
             for (int k = 0; k < p.n_res; ++k) {
@@ -183,8 +180,19 @@ __global__ void __launch_bounds__(UMMA_THREADS) umma_conv_kernel(const __grid_co
                 for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(lrelu(v[2 * i], p.out_slope), lrelu(v[2 * i + 1], p.out_slope));
                 *(uint4*)(p.out_bf16 + o) = *(const uint4*)h;
             }
-            }   // !out_wave
-            }   // valid
+        };
+        for (int blk = 0; blk < p.n_blk; ++blk) {
+            const int row = l0 + blk * VO2W_TILE_M + q;
+            const bool valid = row < p.M_valid;
+            const uint32_t t_blk = t_row + (uint32_t)(blk * p.n_cols);
+            for (int g = 0; g < p.n_cols; g += 8) {
+                uint32_t r[8];
+                __syncwarp();                                // tcgen05.ld is warp-collective (.sync.aligned)
+                tmem_ld8(t_blk + (uint32_t)g, r);
+                tmem_ld_wait();
+                if (valid) emit8(r, g, row);
+                if (p.out_wave) break;                       // conv_post: only column 0 exists
+            }
         }
     }
 

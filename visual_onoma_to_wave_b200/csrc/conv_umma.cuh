@@ -38,8 +38,9 @@ struct UConv {
     int32_t n_kblocks;         // Cin / (16 * kb_steps)
     int32_t Lp_in;             // padded length of the operand buffers
     int32_t M_valid;           // accumulator rows that exist (input time axis length)
+    int32_t n_blk;             // 128-row blocks per CTA (they share every weight stage); block b accumulates at column b * n_cols
     int32_t n_cols;            // accumulator columns of one N-tile
-    int32_t tmem_cols;         // power of two >= max(32, n_cols)
+    int32_t tmem_cols;         // power of two >= max(32, n_blk * n_cols)
     uint32_t a_bytes;          // shared memory reserved for the staged input tile
     uint32_t stage_bytes;      // shared memory per weight stage
     // ---- epilogue ----

@@ -143,37 +143,56 @@ int launch_layers(const PackedLayer* const* layers, const __nv_bfloat16* const* 
     p.n_seg = n_seg;
     p.Cin = L0.Cin;
     p.n_cols = L0.n_cols;
-    int rows_max = 0, n_max = 0;
+    int n_max = 0, halo_max = 0;
     for (int s = 0; s < n_seg; ++s) {
         const PackedLayer& L = *layers[s];
         VO2W_REQUIRE(L.Cin == L0.Cin && L.n_cols == L0.n_cols && L.n_tiles == L0.n_tiles && L.up_s == L0.up_s &&
                          L.Cout == L0.Cout,
                      "launch_layers: fused segments must share their shape");
+        for (int i = 0; i < L.n_items; ++i) n_max = std::max(n_max, L.items[i].n_size);
+        halo_max = std::max(halo_max, L.halo_l + L.halo_r);
+    }
+    // Row blocks per CTA: every weight stage then serves n_blk x 128 rows.  Measured on B200: it pays only where
+    // the per-CTA work is tiny (conv_post: 16 accumulator columns, 14 MMAs per 128 rows -> 142 us became 103 us);
+    // for the upsamplers the many small CTAs per SM (TMEM and shared memory allow up to 8) hide more latency than
+    // the larger tiles save, so they keep n_blk = 1.
+    const int steps = p.Cin / 16;
+    auto stage_for = [&](int n_blk, size_t limit) {
+        const size_t a_bytes = (size_t)p.Cin * (VO2W_TILE_M * n_blk + halo_max) * 2;
+        for (int c = std::min(steps, 8); c >= 1; --c) {
+            if (steps % c) continue;
+            const size_t stage = (size_t)n_max * 32 * c;
+            if (stage <= 48 * 1024 && a_bytes + UMMA_STAGES * stage <= limit) return c;
+        }
+        return 0;
+    };
+    int n_blk = 1, ks = 0;
+    for (int nb = 8; nb >= 1; nb >>= 1) {
+        if (nb * p.n_cols > 512 || (nb > 1 && p.n_cols > 16)) continue;
+        const long long ctas = (long long)vo2w_ceil_div(L_in, VO2W_TILE_M * nb) * L0.n_tiles * B;
+        if (nb > 1 && ctas < 2 * 148) continue;
+        const int c = stage_for(nb, 110 * 1024);
+        if (c) { n_blk = nb; ks = c; break; }
+    }
+    if (!ks) ks = stage_for(1, UMMA_SMEM_LIMIT);
+    p.n_blk = n_blk;
+    int rows_max = 0;
+    for (int s = 0; s < n_seg; ++s) {
+        const PackedLayer& L = *layers[s];
         USeg& sg = p.seg[s];
         sg.in = ins[s];
         sg.w = L.w_dev;
         sg.w_tile_stride = L.w_tile_stride;
         sg.n_items = L.n_items;
         sg.halo_l = L.halo_l;
-        sg.rows = VO2W_TILE_M + L.halo_l + L.halo_r;
+        sg.rows = VO2W_TILE_M * n_blk + L.halo_l + L.halo_r;
         for (int i = 0; i < L.n_items; ++i) {
             sg.items[i] = L.items[i];
             if (s > 0) sg.items[i].zero_init = 0;     // later segments accumulate on top
-            n_max = std::max(n_max, L.items[i].n_size);
         }
         rows_max = std::max(rows_max, sg.rows);
     }
     p.a_bytes = (uint32_t)(p.Cin * rows_max * 2);
-    const int steps = p.Cin / 16;
-    int ks = 0;
-    // prefer a footprint that lets two CTAs share an SM (their copy / MMA / epilogue phases then overlap)
-    const size_t limits[2] = {110 * 1024, UMMA_SMEM_LIMIT};
-    for (int pass = 0; pass < 2 && !ks; ++pass)
-        for (int c = std::min(steps, 8); c >= 1; --c) {
-            if (steps % c) continue;
-            const size_t stage = (size_t)n_max * 32 * c;
-            if (stage <= 48 * 1024 && p.a_bytes + UMMA_STAGES * stage <= limits[pass]) { ks = c; break; }
-        }
     VO2W_REQUIRE(ks > 0, "launch_layers: tile does not fit shared memory (Cin %d rows %d)", p.Cin, rows_max);
     p.kb_steps = ks;
     p.n_kblocks = steps / ks;
@@ -181,7 +200,7 @@ int launch_layers(const PackedLayer* const* layers, const __nv_bfloat16* const* 
     p.Lp_in = (int)vo2w_padded_len(L_in);
     p.M_valid = L_in;
     int tc = 32;
-    while (tc < p.n_cols) tc <<= 1;
+    while (tc < p.n_blk * p.n_cols) tc <<= 1;
     p.tmem_cols = tc;
     p.bias = ep.bias ? ep.bias : L0.bias_dev;
     p.n_res = ep.n_res;
@@ -197,7 +216,7 @@ int launch_layers(const PackedLayer* const* layers, const __nv_bfloat16* const* 
     p.phases_per_tile = L0.phases_per_tile;
     p.L_out = L_in * L0.up_s;
     p.Lp_out = (int)vo2w_padded_len(p.L_out);
-    return umma_conv_launch(p, vo2w_ceil_div(L_in, VO2W_TILE_M), L0.n_tiles, B, st);
+    return umma_conv_launch(p, vo2w_ceil_div(L_in, VO2W_TILE_M * p.n_blk), L0.n_tiles, B, st);
 }
 
 // Host-only probe of the packing logic (no device needed): lets the CPU test-suite replay the
