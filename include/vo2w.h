@@ -94,6 +94,15 @@ int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_host, int B,
                                 void* workspace, size_t workspace_bytes, int ws_fresh,
                                 void* mel_dev, void* wav_dev, void* stream);
 
+/* Same, but returns once the copies and kernels are queued on `stream` (no synchronisation): the caller
+ * overlaps the host<->device copies of one sub-batch with the kernels of another by alternating two
+ * streams, each with its own workspace and staging buffers, and synchronises the stream before reading
+ * wav_host / reusing mel_host.  Host buffers should be pinned for the copies to be asynchronous. */
+int vo2w_generator_forward_host_async(vo2w_generator* g, const float* mel_host, int B, int T,
+                                      float* wav_host, int16_t* wav_i16_host, float max_wav_value,
+                                      void* workspace, size_t workspace_bytes, int ws_fresh,
+                                      void* mel_dev, void* wav_dev, void* stream);
+
 /* Per-layer probe used by the known-answer tests: copies the fp32 activation named
  * `tap` ("conv_pre", "ups.0", "resblocks.3", "mrf.1", ...) of the LAST forward into
  * out_host as NCL [B,C,L].  Returns the element count, or a negative error. */

@@ -299,6 +299,23 @@ def test_weight_norm_checkpoint_and_vocoder_infer_golden(dev, golden_dir):
     np.testing.assert_allclose(i16_dev[0], (g["wav0"] * 32768.0).astype("int16"), atol=4)
 
 
+def test_host_pipeline_matches_single_call(dev, gens):
+    """vocoder_infer over host mels: the two-stream sub-batch pipeline (vo2w_generator_forward_host_async) returns
+    exactly what one synchronous host call and the device path return, including a ragged last sub-batch."""
+    gen = gens[0]["bf16"]
+    mel = synthetic_mel(5, 40, seed=3)
+    ref = gen(mel.to(dev)).squeeze(1).cpu()
+    one = gen.infer_host(mel).clone()
+    assert not gen.host_out_owned
+    assert torch.equal(one, ref)
+    for sub in (2, 4):
+        piped = gen.infer_host(mel, sub_batch=sub)
+        assert gen.host_out_owned and torch.equal(piped, ref)
+    i16 = gen.infer_host(mel, int16_scale=32768.0, sub_batch=2)
+    assert i16.dtype == torch.int16
+    assert torch.equal(i16, torch.from_numpy((ref.numpy() * np.float32(32768.0)).astype("int16")))
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

@@ -1,6 +1,9 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-TAG=new timeout 200 python tools/launch_times.py 64 2>&1 | grep -v Removing | tee gpurun_out/exp.log
-TAG=b16 timeout 200 python tools/launch_times.py 16 2>&1 | grep -v Removing | tee -a gpurun_out/exp.log
+
+
+
+for sb in 64 128 256; do timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --sub-batch $sb 2>&1 | grep "^{" | python -c "
+import json,sys
+d=json.loads(sys.stdin.readline()); print('sub', d['config']['sub_batch'], 'value', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'], d['clocks'])"; done

@@ -38,6 +38,9 @@ SYMBOLS = {
     "vo2w_generator_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                               C.c_float, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
                                               C.c_void_p]),
+    "vo2w_generator_forward_host_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_float, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p]),
     "vo2w_generator_debug_tap": (C.c_longlong, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t]),
     "vo2w_debug_layer": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                    C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),

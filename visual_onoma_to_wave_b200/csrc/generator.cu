@@ -460,10 +460,9 @@ __global__ void wav_to_i16_kernel(const float* __restrict__ w, short* __restrict
 }
 }  // namespace
 
-extern "C" int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
-                                           int16_t* wav_i16_host, float max_wav_value, void* workspace,
-                                           size_t workspace_bytes, int ws_fresh, void* mel_dev, void* wav_dev,
-                                           void* stream) {
+static int forward_host_impl(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
+                             int16_t* wav_i16_host, float max_wav_value, void* workspace, size_t workspace_bytes,
+                             int ws_fresh, void* mel_dev, void* wav_dev, void* stream, bool sync) {
     VO2W_REQUIRE(g && mel_host && mel_dev && wav_dev, "generator_forward_host: null argument");
     VO2W_REQUIRE(wav_host || wav_i16_host, "generator_forward_host: no output buffer");
     VO2W_REQUIRE(B > 0 && T > 0, "generator_forward_host: empty batch");
@@ -485,8 +484,24 @@ extern "C" int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_h
         VO2W_CUDA_OK(cudaMemcpyAsync(wav_i16_host, workspace, (size_t)n_out * 2, cudaMemcpyDeviceToHost, st));
     }
     if (wav_host) VO2W_CUDA_OK(cudaMemcpyAsync(wav_host, wav_dev, (size_t)n_out * 4, cudaMemcpyDeviceToHost, st));
-    VO2W_CUDA_OK(cudaStreamSynchronize(st));
+    if (sync) VO2W_CUDA_OK(cudaStreamSynchronize(st));
     return VO2W_OK;
+}
+
+extern "C" int vo2w_generator_forward_host(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
+                                           int16_t* wav_i16_host, float max_wav_value, void* workspace,
+                                           size_t workspace_bytes, int ws_fresh, void* mel_dev, void* wav_dev,
+                                           void* stream) {
+    return forward_host_impl(g, mel_host, B, T, wav_host, wav_i16_host, max_wav_value, workspace, workspace_bytes, ws_fresh,
+                             mel_dev, wav_dev, stream, true);
+}
+
+extern "C" int vo2w_generator_forward_host_async(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
+                                                 int16_t* wav_i16_host, float max_wav_value, void* workspace,
+                                                 size_t workspace_bytes, int ws_fresh, void* mel_dev, void* wav_dev,
+                                                 void* stream) {
+    return forward_host_impl(g, mel_host, B, T, wav_host, wav_i16_host, max_wav_value, workspace, workspace_bytes, ws_fresh,
+                             mel_dev, wav_dev, stream, false);
 }
 
 extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap, float* out_host, size_t capacity) {

@@ -127,6 +127,8 @@ class Generator(nn.Module):
         self._ws = OrderedDict()        # (B,T) -> workspace tensor (zero halo rows are an invariant of ours)
         self._host = {}                 # (B,T) -> pinned staging for the host-buffer call
         self.last_launches = 0
+        self.host_sub_batch = 64
+        self._pipe = None
 
     # ---- reference surface -------------------------------------------------------------
     def remove_weight_norm(self):
@@ -176,11 +178,15 @@ class Generator(nn.Module):
     def hop(self) -> int:
         return int(math.prod(self.h.upsample_rates))
 
-    def infer_host(self, mel_host: torch.Tensor, device=None, int16_scale: float | None = None):
-        """Host mel [B,80,T] -> host wav (pinned) through vo2w_generator_forward_host.
+    def infer_host(self, mel_host: torch.Tensor, device=None, int16_scale: float | None = None,
+                   sub_batch: int | None = None):
+        """Host mel [B,80,T] -> host wav through the C ABI's host-buffer entry points.
 
-        Copies H2D, runs, copies D2H and synchronises inside the C call.  Returns a float32
-        [B, T*hop] tensor, or int16 when ``int16_scale`` (max_wav_value) is given.
+        Up to ``sub_batch`` (default ``self.host_sub_batch`` = 64) utterances: one vo2w_generator_forward_host call
+        (H2D, kernels, D2H, synchronise) into a pinned buffer owned by the generator.  Larger batches are walked in
+        sub-batches on two alternating CUDA streams (vo2w_generator_forward_host_async), each with its own
+        workspace and pinned staging, so the copies of one sub-batch overlap the kernels of the other; the result is
+        a fresh host tensor.  Returns float32 [B, T*hop], or int16 when ``int16_scale`` (max_wav_value) is given.
         """
         if mel_host.is_cuda or mel_host.dtype != torch.float32 or mel_host.dim() != 3 or mel_host.shape[1] != 80:
             raise RuntimeError("infer_host expects a CPU float32 mel [B,80,T]")
@@ -189,6 +195,10 @@ class Generator(nn.Module):
             raise RuntimeError("infer_host: the vocoder must live on a CUDA device (no CPU fallback)")
         B, _, T = mel_host.shape
         mel_host = mel_host.contiguous()
+        sub = int(sub_batch or self.host_sub_batch)
+        self.host_out_owned = B > sub             # False: the result aliases a pinned buffer reused by the next call
+        if B > sub:
+            return self._infer_host_pipelined(mel_host, device, int16_scale, sub)
         lib = _lib.lib()
         with torch.cuda.device(device):
             handle = self._get_handle(device)
@@ -208,6 +218,57 @@ class Generator(nn.Module):
                                                        mel_dev.data_ptr(), wav_dev.data_ptr(), stream),
                        "vo2w_generator_forward_host")
             self.last_launches = lib.vo2w_generator_last_launches(handle)
+        return out
+
+    def _infer_host_pipelined(self, mel_host, device, int16_scale, sub):
+        lib = _lib.lib()
+        B, _, T = mel_host.shape
+        odt = torch.int16 if int16_scale is not None else torch.float32
+        n_out = T * self.hop
+        out = torch.empty(B, n_out, dtype=odt)
+        with torch.cuda.device(device):
+            handle = self._get_handle(device)
+            key = (sub, T, device.index, odt)
+            if self._pipe is None or self._pipe[0] != key:
+                need = lib.vo2w_generator_workspace_bytes(handle, sub, T)
+                slots = []
+                for _ in range(2):
+                    slots.append({"stream": torch.cuda.Stream(device), "ws": torch.empty(need, dtype=torch.uint8, device=device),
+                                  "mel": torch.empty(sub, 80, T, device=device), "wav": torch.empty(sub, n_out, device=device),
+                                  "pin": torch.empty(sub, n_out, dtype=odt).pin_memory(), "shape": None, "pending": None})
+                self._pipe = (key, slots)
+            slots = self._pipe[1]
+            cur = torch.cuda.current_stream(device)
+            for sl in slots:
+                sl["stream"].wait_stream(cur)
+            launches = 0
+
+            def retire(sl):
+                if sl["pending"] is not None:
+                    a, b = sl["pending"]
+                    sl["stream"].synchronize()
+                    out[a:b].copy_(sl["pin"][: b - a])       # host copy; the other stream's kernels keep running
+                    sl["pending"] = None
+
+            for i, a in enumerate(range(0, B, sub)):
+                b = min(a + sub, B)
+                sl = slots[i & 1]
+                retire(sl)
+                fresh = sl["shape"] != (b - a, T)            # the workspace layout depends on the batch size
+                sl["shape"] = (b - a, T)
+                src = mel_host[a:b]
+                f32_ptr = None if int16_scale is not None else sl["pin"].data_ptr()
+                i16_ptr = sl["pin"].data_ptr() if int16_scale is not None else None
+                _lib.check(lib.vo2w_generator_forward_host_async(handle, src.data_ptr(), b - a, T, f32_ptr, i16_ptr,
+                                                                 float(int16_scale or 0.0), sl["ws"].data_ptr(), sl["ws"].numel(),
+                                                                 int(fresh), sl["mel"].data_ptr(), sl["wav"].data_ptr(),
+                                                                 sl["stream"].cuda_stream),
+                           "vo2w_generator_forward_host_async")
+                launches += lib.vo2w_generator_last_launches(handle)
+                sl["pending"] = (a, b)
+            for sl in slots:
+                retire(sl)
+            self.last_launches = launches
         return out
 
     def debug_tap(self, name: str) -> torch.Tensor:
@@ -285,6 +346,7 @@ class Generator(nn.Module):
         if hasattr(self, "_ws"):
             self._ws.clear()
             self._host.clear()
+            self._pipe = None
 
     def _get_handle(self, device):
         key = (device.index if device.index is not None else torch.cuda.current_device(), self.precision)

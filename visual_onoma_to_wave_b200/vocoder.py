@@ -57,8 +57,8 @@ def vocoder_infer(mels, vocoder, model_config, preprocess_config, lengths=None, 
         scale = preprocess_config["preprocessing"]["audio"]["max_wav_value"]
     with torch.no_grad():
         if not mels.is_cuda:
-            out = vocoder.infer_host(mels.float(), int16_scale=scale).numpy()
-            wavs = out.copy()
+            out = vocoder.infer_host(mels.float(), int16_scale=scale)
+            wavs = out.numpy() if vocoder.host_out_owned else out.numpy().copy()
         else:
             wavs = vocoder(mels).squeeze(1)
             if Normalize:
