@@ -7,7 +7,7 @@
 Workload = BASELINE.json configs[3] ("batch-sharded vocoder inference, 1024 utterances x 2 s across
 1/2/4/8 B200"), the configuration the metric "vocoder audio-sec/sec at 1/2/4/8 B200" is quoted on:
 a step is one pass of Generator.forward over all 1024 synthetic [80,172] mels, the utterances split
-contiguously over the ranks (strong scaling, no data-path collective), each rank walking its shard in
+contiguously over the ranks (no data-path collective), each rank walking its shard in
 sub-batches.  One JSON line on rank 0.
 """
 from __future__ import annotations
@@ -121,7 +121,7 @@ def run_reference(args):
     sample = f"{n_utt} of the {N_UTT} utterances x {T_FRAMES} frames per step (bounded sample of the same workload)"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "strong",
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
         "config": {"workload": "configs[3]: batch-sharded vocoder inference, 1024 utterances x 2 s (T=172), HiFi-GAN V1, random-init",
                    "sample": sample, "host_threads": torch.get_num_threads()},
@@ -179,7 +179,10 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
 
-    lo, hi = shard_bounds(N_UTT, world, rank)
+    # weak scaling (default): every rank holds configs[3]'s 1024 utterances, the job is the 1024 * N utterance batch
+    # split contiguously; --scaling strong keeps the job at 1024 utterances in total
+    n_job = N_UTT * world if args.scaling == "weak" else N_UTT
+    lo, hi = shard_bounds(n_job, world, rank)
     n_local = hi - lo
     sub = min(args.sub_batch, n_local)
     gen = v.Generator(v.AttrDict(V1_CONFIG), precision=args.precision)
@@ -188,7 +191,7 @@ def run_ours(args):
     gen.load_state_dict(seeded_state_dict(1234))
     gen.to(dev)
     gen.host_sub_batch = sub
-    mel_host = synthetic_mel(N_UTT, T_FRAMES, seed=0)[lo:hi].contiguous().pin_memory()
+    mel_host = synthetic_mel(N_UTT, T_FRAMES, seed=0)[[i % N_UTT for i in range(lo, hi)]].contiguous().pin_memory()
     mel_dev = mel_host.to(dev)
     chunks = [(a, min(a + sub, n_local)) for a in range(0, n_local, sub)]
     cfg_m = {"vocoder": {"model": "HiFi-GAN"}}
@@ -235,7 +238,7 @@ def run_ours(args):
     launches_per_step = gen.last_launches * len(chunks)
     _, e2e_wall_ms, _ = timed(step_e2e, args.steps, 1)
 
-    total_audio_s = N_UTT * AUDIO_S_PER_UTT
+    total_audio_s = n_job * AUDIO_S_PER_UTT
     ms_per_step = dev_ms / args.steps
     value = total_audio_s / (ms_per_step * 1e-3)
     e2e_value = total_audio_s / (e2e_wall_ms / args.steps * 1e-3)
@@ -267,9 +270,11 @@ def run_ours(args):
                 "peak_source": f"bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json (kernel timed inside a long step)",
                 "traffic": None, **per_launch}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(prof):
-        try:
-            roofline["traffic"] = json.load(open(prof)).get("pair_umma_kernel_dram_bytes_per_launch")
+    if os.path.exists(prof) and args.precision == "bf16":
+        try:   # ncu --set full capture at batch tj["batch"]; DRAM bytes scale linearly with the utterances of a launch
+            tj = json.load(open(prof))
+            roofline["traffic"] = tj["pair_umma_kernel_dram_bytes_per_launch"] * (b - a) / tj["batch"]
+            roofline["traffic_source"] = tj["source"]
         except Exception:
             pass
 
@@ -289,19 +294,19 @@ def run_ours(args):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": args.precision, "data": "synthetic",
             "config": {"workload": "configs[3]: batch-sharded vocoder inference, 1024 utterances x 2 s (T=172 frames -> 44032 samples), "
-                                   "HiFi-GAN V1 Generator.forward, random-init weights (seed 1234), utterances split contiguously over ranks",
-                       "utterances": N_UTT, "frames": T_FRAMES, "sub_batch": sub, "parallelism": f"utterance-shard x{world}",
+                                   "HiFi-GAN V1 Generator.forward, random-init weights (seed 1234); " + ("weak scaling: 1024 utterances per GPU, the 1024 x N job split contiguously over ranks" if args.scaling == "weak" else "strong scaling: 1024 utterances in total split contiguously over ranks"),
+                       "utterances": n_job, "utterances_per_gpu": n_local, "frames": T_FRAMES, "sub_batch": sub, "parallelism": f"utterance-shard x{world}",
                        "precision_mode": args.precision,
                        "l2": "no flush: each step streams >100 GB of activations per GPU through a 126 MB L2; inputs (56 MB) do not survive"},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": N_UTT * 80 * T_FRAMES * 4,
-                    "d2h_bytes_per_step": N_UTT * T_FRAMES * HOP * 4,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n_job * 80 * T_FRAMES * 4,
+                    "d2h_bytes_per_step": n_job * T_FRAMES * HOP * 4,
                     "api": "vocoder_infer(host mels of the whole shard) -> vo2w_generator_forward_host_async per sub-batch on two alternating streams (pinned H2D, kernels, D2H), numpy out, wall clock"},
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "tflops": FLOP_PER_FRAME * N_UTT * T_FRAMES / (ms_per_step * 1e-3) / 1e12, "extra": extra,
+            "tflops": FLOP_PER_FRAME * n_job * T_FRAMES / (ms_per_step * 1e-3) / 1e12, "extra": extra,
         }
         print(json.dumps(line))
     if world > 1:
@@ -319,6 +324,8 @@ def main():
     ap.add_argument("--sub-batch", type=int, default=128)
     ap.add_argument("--ref-utts", type=int, default=16, help="utterances per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 1024 utterances per GPU (job = 1024 x N); strong: 1024 utterances in total")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -15,4 +15,6 @@ echo "ncu launches rc=$?"
 timeout 300 python tools/profile_target.py 2 $B > gpurun_out/plain2.log 2>&1 &&
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:pair_umma -s 28 -c 28 -o gpurun_out/prof -f python tools/profile_target.py 2 $B > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
+# the report itself can exceed what gpurun copies back: keep the raw page as CSV
+ncu -i gpurun_out/prof.ncu-rep --page raw --csv > gpurun_out/prof_raw.csv 2>/dev/null; rm -f gpurun_out/prof.ncu-rep
 fi
