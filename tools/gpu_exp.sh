@@ -1,9 +1,4 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-
-
-
-for sb in 64 128 256; do timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --sub-batch $sb 2>&1 | grep "^{" | python -c "
-import json,sys
-d=json.loads(sys.stdin.readline()); print('sub', d['config']['sub_batch'], 'value', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'], d['clocks'])"; done
+VO2W_PAIR_PROF=1 VO2W_PAIR_TRACE=1 timeout 300 python tools/profile_target.py 1 64 > gpurun_out/trace.log 2>&1; echo "rc=$?"

@@ -128,6 +128,55 @@ __global__ void __launch_bounds__(128) bench_kernel(const BenchP p, unsigned lon
     }
 }
 
+// Queue-depth probe: one thread issues `n` MMAs (cg=2, N=32, 4 accumulators) back to back and reads the clock right
+// after the last issue (before any completion wait), then waits for completion.  issue_cycles ~ 0 for small n
+// if the tensor pipe queues instructions; the knee is the queue depth.
+__global__ void __launch_bounds__(128) queue_kernel(int n, unsigned long long* out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bars[2];
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5;
+    uint32_t cta_rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    for (int i = threadIdx.x; i < (96 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x3c003c00u;
+    fence_proxy_async();
+    const uint32_t bar0 = smem_u32(bars);
+    if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); fence_mbar_init(); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    if (warp == 1 && cta_rank == 0) {
+        constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24) | (1u << 7) | (1u << 10);
+        const uint64_t a0 = umma_smem_desc(smem_u32(smem), 514u * 16u, 128u), b0 = umma_smem_desc(smem_u32(smem) + 64 * 1024, 16u * 16u, 128u);
+        if (elect_one()) {
+            const long long t0 = clock64();
+            for (int i = 0; i < n; ++i) mma_ss<2, false>(tmem_base + (uint32_t)((i & 3) * 32), a0 + (uint64_t)((i & 3) * 128), b0, idesc);
+            const long long t1 = clock64();
+            commit<2>(bar0);
+            mbar_wait(bar0, 0);
+            const long long t2 = clock64();
+            // cost of polling barriers that are already complete, and of a cluster-mapped remote arrive
+            for (int i = 0; i < 8; ++i) mbar_wait(bar0, 0);
+            const long long t3 = clock64();
+            for (int i = 0; i < 8; ++i) commit<2>(bar0 + 8);
+            const long long t4 = clock64();
+            if (blockIdx.x == 0) { out[0] = (unsigned long long)(t1 - t0); out[1] = (unsigned long long)(t2 - t0);
+                                   out[2] = (unsigned long long)(t3 - t2); out[3] = (unsigned long long)(t4 - t3); }
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+}
+
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
 
 template <int CG, int M, int N, bool TS, bool TF32, int NACC, int SHIFT, int AROWS = 0>
@@ -184,6 +233,27 @@ int main(int argc, char** argv) {
     const int n_sm = prop.multiProcessorCount;
     printf("device %s, %d SMs, cc %d.%d\n", prop.name, n_sm, prop.major, prop.minor);
     const int bt = argc > 1 ? atoi(argv[1]) : 2048;
+    if (argc > 2 && argv[2][0] == 'q') {   // tensor-pipe queue depth
+        unsigned long long* d;
+        CK(cudaMalloc(&d, 32));
+        CK(cudaFuncSetAttribute(queue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 97 * 1024));
+        for (int n : {1, 2, 4, 8, 12, 16, 24, 32, 48, 64, 128}) {
+            unsigned long long h[4];
+            for (int rep = 0; rep < 2; ++rep) {
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(2); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = 97 * 1024;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                CK(cudaLaunchKernelEx(&cfg, queue_kernel, n, d));
+                CK(cudaDeviceSynchronize());
+            }
+            CK(cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost));
+            printf("queue probe: %3d MMAs (cg=2 N=32): issue loop %6llu cycles, until complete %6llu cycles; 8 polls of a complete barrier %llu, 8 commits %llu\n", n, h[0], h[1], h[2], h[3]);
+        }
+        return 0;
+    }
     if (argc > 2) {   // the fused kernel's operand patterns only
         run<2, 256, 32, false, false, 1, 0>("2CTA SS", bt, n_sm);
         run<2, 256, 32, false, false, 4, 0>("2CTA SS 4acc", bt, n_sm);

@@ -171,7 +171,7 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
 
 // VO2W_PAIR_PROF=1: event trace of CTA 0 (the leader of pair 0): trace[role][unit][2] timestamps (clock64)
 #define PAIR_TR_UNITS 48
-#define PAIR_TR_ROLES 8     // 0 input producer, 1 conv1 issue, 2 conv2 issue, 3 e1, 4 e2, 5 weight producer
+#define PAIR_TR_ROLES 10     // 0 input producer, 1 conv1 issue, 2 conv2 issue, 3 e1, 4 e2, 5 weight producer
 __device__ __forceinline__ void trace(const PairP& p, int role, int unit, int slot) {
     if (p.prof && blockIdx.x == 0 && unit < PAIR_TR_UNITS && (threadIdx.x & 31) == 0)
         p.prof[(size_t)gridDim.x * 16 + ((size_t)role * PAIR_TR_UNITS + unit) * 2 + slot] = (unsigned long long)clock64();
@@ -199,6 +199,8 @@ __device__ __forceinline__ void mma_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t 
 // keep:   accumulate on top of what the accumulators hold (conv2 of segments after the first).
 // The whole warp walks the (warp-uniform) loops so that addresses stay in uniform registers; one elected
 // lane issues.  NI issuer warps split the row blocks (issue, not execution, limits the small-N stages).  All descriptor arithmetic is in 16-byte units on the low descriptor word.
+// Runs in ONE thread (the elected lane of an issuer warp): the tensor pipe queues ~24 MMAs, so a thread that issues
+// them a few cycles apart runs ahead of the pipe and its barrier waits / commits overlap queued work.
 template <int CG, int C, int NB, int KS, int NI>
 __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int issuer, uint32_t bar0, uint32_t a_addr, uint32_t a_rows,
                                            int n_items, int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
@@ -207,14 +209,25 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
     constexpr uint32_t n_loc = (uint32_t)C / CG;
     constexpr uint32_t KB = C < 64 ? C : 64;
     constexpr uint32_t item_units = n_loc * KB * 2u / 16u;                    // 16-byte units of one weight item
-    const uint32_t a_base = ((a_addr >> 4) & 0x3FFFu) | (a_rows << 16);      // LBO = a_rows * 16 B
     constexpr uint32_t b_lbo_field = n_loc << 16;                             // LBO = n_loc * 16 B
-    uint32_t tap = 0, kb = 0;                                                 // items 1.. run kb-major: (kb, tap)
+    constexpr int MY = NB / NI;                                               // row blocks of this issuer
+    const uint32_t a_base = ((a_addr >> 4) & 0x3FFFu) | (a_rows << 16);      // LBO = a_rows * 16 B
     const uint32_t kb_rows = (KB >> 3) * a_rows;                              // 16-byte units per 64-channel block
     const uint32_t blk_back = second ? 2u * (uint32_t)p.h2max : 0u;
     const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_shift = (uint32_t)p.slots_log2;
     const int per_stage = p.items_per_stage;
     const bool no_mma = (p.dbg & 4) != 0;
+    // per (row block, K step) offsets of the A descriptor and the accumulators of this issuer: loop invariants
+    uint32_t a_off[MY][KS], d_blk[MY];
+#pragma unroll
+    for (int bi = 0; bi < MY; ++bi) {
+        const int blk = issuer + bi * NI;
+        d_blk[bi] = d_tmem + (uint32_t)(blk * C);
+#pragma unroll
+        for (int s = 0; s < KS; ++s) a_off[bi][s] = (uint32_t)(blk * 128) - (blk > 0 ? blk_back : 0u) + (uint32_t)s * 2u * a_rows;
+    }
+    uint32_t tap = 0, kb = 0;                                                 // items 1.. run kb-major: (kb, tap)
+    uint32_t a_lo = a_base;                                                   // descriptor low word of (kb, tap), block 0, step 0
     int item = 0;
     while (item < n_items) {
         const uint32_t slot = wit & slot_mask, par = (wit >> slot_shift) & 1u;
@@ -222,25 +235,18 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
         if (prof) tw = clock64();
         mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
         if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL_PEER + slot), par);
-        if (prof) w_wait += clock64() - tw;
-        __syncwarp();
-        tc_fence_after();
-        if (prof && tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0);
+        if (prof) { w_wait += clock64() - tw; if (tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0); }
         const int cnt = min(per_stage, n_items - item);
-        const uint32_t stage_lo = (((ring_addr + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
-        for (int i = 0; i < cnt; ++i) {
-            const int idx = item + i;
-            const uint32_t b_lo = stage_lo + (uint32_t)i * item_units;
-            if (idx == 0) {
-                // item 0 is the bias: D = ones[128 x 16] . (b_hi, b_lo, 0, ...)^T initialises the accumulators
-                if (elect_one()) {
+        uint32_t b_lo = (((ring_addr + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
+        int i = 0;
+        if (item == 0) {
+            // item 0 is the bias: D = ones[128 x 16] . (b_hi, b_lo, 0, ...)^T initialises the accumulators
 #pragma unroll
-                    for (int bi = 0; bi < NB / NI; ++bi)
-                        mma_lo<CG>(d_tmem + (uint32_t)((issuer + bi * NI) * C), ones_lo, b_lo, idesc, keep ? 1u : 0u);
-                }
-                __syncwarp();
-                continue;
-            }
+            for (int bi = 0; bi < MY; ++bi) mma_lo<CG>(d_blk[bi], ones_lo, b_lo, idesc, keep ? 1u : 0u);
+            b_lo += item_units;
+            i = 1;
+        }
+        for (; i < cnt; ++i) {
             if (second && tap == 0) {
                 // conv2 reads channel block kb of the operand buffer: wait until e1 has written it (the later
                 // blocks are still being converted while these MMAs run)
@@ -248,28 +254,22 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
                 if (prof) tt = clock64();
                 mbar_wait_cluster(t_bar + 8u * kb, t_parity);
                 if (prof) t_wait += clock64() - tt;
-                __syncwarp();
                 tc_fence_after();
             }
-            const uint32_t a_lo = a_base + kb * kb_rows + tap * (uint32_t)dil;
-            if (!no_mma && elect_one()) {
+            if (!no_mma) {
 #pragma unroll
-                for (int bi = 0; bi < NB / NI; ++bi) {
-                    const int blk = issuer + bi * NI;                       // this issuer's row blocks
-                    const uint32_t a_blk = a_lo + (uint32_t)(blk * 128) - (blk > 0 ? blk_back : 0u);
+                for (int bi = 0; bi < MY; ++bi) {
 #pragma unroll
                     for (int s = 0; s < KS; ++s)
-                        mma_lo<CG>(d_tmem + (uint32_t)(blk * C), a_blk + (uint32_t)s * 2u * a_rows,
-                                   b_lo + (uint32_t)s * 2u * n_loc, idesc, 1u);
+                        mma_lo<CG>(d_blk[bi], a_lo + a_off[bi][s], b_lo + (uint32_t)s * 2u * n_loc, idesc, 1u);
                 }
             }
-            __syncwarp();
-            if (++tap == (uint32_t)k_taps) { tap = 0; ++kb; }
+            b_lo += item_units;
+            a_lo += (uint32_t)dil;
+            if (++tap == (uint32_t)k_taps) { tap = 0; ++kb; a_lo = a_base + kb * kb_rows; }
         }
         if (prof && tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 1);
-        if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
-        __syncwarp();
-        if (prof && tr_unit >= 0 && item == 0) trace(p, 7, tr_unit, 0);
+        mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
         item += cnt;
         ++wit;
     }
@@ -365,11 +365,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             auto feed = [&](int n, int s, int conv) {
                 const PairSegP& sg = p.seg[s];
                 const uint8_t* base = (conv ? sg.w2 : sg.w1) + (size_t)rank * sg.conv_bytes_rank;
-                trace(p, 5, n, conv);
                 for (int item = 0; item < sg.n_items; item += p.items_per_stage, ++wit) {
                     const int cnt = min(p.items_per_stage, sg.n_items - item);
                     const uint32_t slot = wit & slot_mask, use = wit >> slot_shift;
                     if (use > 0) mbar_wait(bar0 + 8u * (BAR_W_EMPTY + slot), (use - 1) & 1u);
+                    if (item == 0) trace(p, 5, n, conv);     // slot free seen = request time of the first stage
                     const uint32_t bytes = (uint32_t)cnt * p.item_bytes;
                     const uint32_t full = bar0 + 8u * (BAR_W_FULL + slot);
                     mbar_arrive_expect_tx(full, bytes);
@@ -401,6 +401,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // In-order execution of one thread's MMAs gives the implicit orderings: conv1(n+ND) is issued after the
         // T_FULL wait of conv2(n) (D1 free), and e1(n+ND) starts after conv1(n+ND), issued after conv2(n) (t free).
         const int issuer = warp - PAIR_WARP_MMA0;
+        if (elect_one()) {
         const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
         const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
         const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(ND * NB * C);
@@ -415,17 +416,17 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const int buf = n & xa_mask, use = n >> xa_shift;
             long long c0 = 0;
             if (prof) c0 = clock64();
+            if (prof && issuer == 0) trace(p, 8, n, 0);
             mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+            if (prof && issuer == 0) trace(p, 8, n, 1);
             if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
+            if (prof && issuer == 0) trace(p, 9, n, 0);
             if (prof) { c_xa += clock64() - c0; if (issuer == 0) trace(p, 1, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
                            d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, issuer == 0 ? n : -1);
-            if (elect_one()) {
-                mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));        // input tile reusable
-                mma_commit<CG>(bar0 + 8u * (BAR_D1_FULL + n % ND));      // e1 may start
-            }
-            __syncwarp();
+            mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));            // input tile reusable
+            mma_commit<CG>(bar0 + 8u * (BAR_D1_FULL + n % ND));          // e1 may start
             if (prof && issuer == 0) trace(p, 1, n, 1);
         };
         auto conv2 = [&](int n, int it, int s) {
@@ -439,10 +440,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
                            true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
                            bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t);
-            if (s == n_seg - 1) {
-                if (elect_one()) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
-                __syncwarp();
-            }
+            if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
             if (prof && issuer == 0) trace(p, 2, n, 1);
         };
         int it2 = 0, s2 = 0;                          // (tile, segment) of the unit conv2 works on
@@ -462,12 +460,14 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 if (++s2 == n_seg) { s2 = 0; ++it2; }
             }
         }
-        if (p.prof && lane == 0 && issuer == 0) {
+        if (p.prof && issuer == 0) {
             unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
             o[0] = (unsigned long long)(clock64() - c_start);
             o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
             o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2;
         }
+        }   // elected thread
+        __syncwarp();
     } else if (warp == PAIR_WARP_MMA0 && rank != 0) {
         if (lane == 0) {
             // ================= peer relay: forward "landed" events to the leader's barriers =================
@@ -912,8 +912,9 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
             auto at = [&](int role, int u, int sl) { return (long long)tr[((size_t)role * PAIR_TR_UNITS + u) * 2 + sl]; };
             const long long t0 = at(1, 16, 0);
             static const char* names[PAIR_TR_ROLES] = {"xa producer (idle, EMPTY seen)", "conv1 issue (start, done)", "conv2 issue (start, done)",
-                                                       "e1 (D1 full seen, done)", "e2 (D2 full seen, done)", "w producer (conv1, conv2)",
-                                                       "conv1 (W seen, items issued)", "conv1 (W_EMPTY committed, -)"};
+                                                       "e1 (D1 full seen, done)", "e2 (D2 full seen, done)", "w producer (request c1, c2)",
+                                                       "conv1 (W seen, items issued)", "conv1 (W_EMPTY committed, -)",
+                                                       "conv1 (before XA wait, XA local seen)", "conv1 (XA peer seen, W local seen)"};
             for (int role = 0; role < PAIR_TR_ROLES; ++role) {
                 fprintf(stderr, "  [trace] %-32s", names[role]);
                 for (int u = 16; u < 28 && u < p.iters * p.n_seg; ++u)
