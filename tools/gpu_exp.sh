@@ -1,4 +1,4 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-VO2W_PAIR_PROF=1 VO2W_PAIR_TRACE=1 timeout 300 python tools/profile_target.py 1 64 > gpurun_out/trace.log 2>&1; echo "rc=$?"
+for l in A B A B; do TAG=lib$l VO2W_LIB=$PWD/tools/lib$l.so timeout 200 python tools/launch_times.py 64 2>&1 | grep -v Removing; done | tee gpurun_out/exp.log

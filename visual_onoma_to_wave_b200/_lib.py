@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvo2w.so")
+LIB_PATH = os.environ.get("VO2W_LIB") or os.path.join(HERE, "libvo2w.so")   # VO2W_LIB: A/B builds in experiments
 
 OK, E_INVALID, E_CUDA, E_WORKSPACE, E_NODEVICE = 0, -1, -2, -3, -4
 DUR_I32, DUR_I64, DUR_F32, DUR_F64 = 0, 1, 2, 3
