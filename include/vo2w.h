@@ -151,6 +151,25 @@ int vo2w_generator_last_launches(const vo2w_generator* g);
 int vo2w_generator_set_timing(vo2w_generator* g, int on);
 int vo2w_generator_get_timing(vo2w_generator* g, float* ms, int32_t* kind, int capacity);
 
+/* ---- mel_linear + PostNet -------------------------------------
+ * Replaces PostNet.forward (scripts/transformer/Layers.py:126-137) in eval mode: x [B,L,n_mel] fp32 ->
+ * 4 x tanh(BatchNorm1d(Conv1d k)) -> BatchNorm1d(Conv1d k) -> [B,L,n_mel].  `folded_host` holds, per convolution,
+ * weight [Cout,Cin,k] then bias [Cout] with the eval-mode BatchNorm already folded in by the caller
+ * (w' = w * g / sqrt(var + eps), b' = (b - mean) * g / sqrt(var + eps) + beta).  add_input != 0 returns
+ * postnet(x) + x, the `postnet_output` of vTTS.forward (scripts/model/vtts.py:107).  fp32 CUDA-core path. */
+typedef struct vo2w_postnet vo2w_postnet;
+int vo2w_postnet_create(int n_mel, int dim, int k, int n_conv, const float* folded_host, size_t n_floats,
+                        vo2w_postnet** out);
+int vo2w_postnet_destroy(vo2w_postnet* p);
+size_t vo2w_postnet_workspace_bytes(const vo2w_postnet* p, int B, int L);
+int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int L, float* out, int add_input,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* nn.Linear on the last axis (mel_linear, scripts/model/vtts.py:106): y[r,:] = W x[r,:] + b for `rows` rows;
+ * x [rows,K], w [N,K], bias [N] or NULL, y [rows,N], all fp32 on the device. */
+int vo2w_linear_forward(const float* x, const float* w, const float* bias, long long rows, int K, int N,
+                        float* y, void* stream);
+
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad
  * (scripts/utils/tools.py:669-687).

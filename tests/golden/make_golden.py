@@ -139,5 +139,33 @@ def main():
     np.savez_compressed(os.path.join(HERE, "length_regulator.npz"), **out)
 
 
+def postnet_golden():
+    """PostNet + mel_linear tail, outputs of the reference's own classes."""
+    from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict
+    from transformer.Layers import PostNet   # reference
+    sd = seeded_postnet_state_dict(4321)
+    pn = PostNet()
+    pn.load_state_dict(sd)                    # strict: the key set is the reference's
+    pn.eval()
+    g = torch.Generator().manual_seed(7)
+    out = {"sd_sha256": np.frombuffer(sd_sha256(sd).encode(), dtype=np.uint8)}
+    with torch.no_grad():
+        for name, (B, L) in {"a": (2, 37), "b": (1, 172), "c": (3, 5)}.items():
+            x = torch.randn(B, L, 80, generator=g) * 2.0 - 3.0          # log-mel-like range
+            out[f"x_{name}"] = x.numpy()
+            out[f"y_{name}"] = pn(x).numpy()
+        lin = torch.nn.Linear(256, 80)
+        lin.weight.data = torch.randn(80, 256, generator=g) / 16.0
+        lin.bias.data = torch.randn(80, generator=g) * 0.1
+        dec = torch.randn(2, 23, 256, generator=g)
+        o = lin(dec)
+        out["lin_w"], out["lin_b"], out["dec"] = lin.weight.data.numpy(), lin.bias.data.numpy(), dec.numpy()
+        out["mel"] = o.numpy()
+        out["postnet_mel"] = (pn(o) + o).numpy()                       # vtts.py:106-107
+    np.savez_compressed(os.path.join(HERE, "postnet.npz"), **out)
+    print("postnet.npz written")
+
+
 if __name__ == "__main__":
     main()
+    postnet_golden()

@@ -316,6 +316,49 @@ def test_host_pipeline_matches_single_call(dev, gens):
     assert torch.equal(i16, torch.from_numpy((ref.numpy() * np.float32(32768.0)).astype("int16")))
 
 
+# ------------------------------------------------------------------------------------------
+# PostNet + mel_linear
+# ------------------------------------------------------------------------------------------
+POSTNET_TOL = 1e-4     # max-abs-err of the fp32 path against the reference's fp32 CPU output (values reach +-5.5)
+
+
+@pytest.mark.gpu
+def test_postnet_and_mel_linear_against_reference_golden(dev, golden_dir):
+    from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict
+    g = np.load(os.path.join(golden_dir, "postnet.npz"))
+    pn = v.PostNet()
+    pn.load_state_dict(seeded_postnet_state_dict(4321))
+    pn.eval().to(dev)
+    for name in "abc":
+        x = torch.from_numpy(g[f"x_{name}"]).to(dev)
+        y = pn(x).cpu()
+        assert y.shape == x.shape
+        assert float((y - torch.from_numpy(g[f"y_{name}"])).abs().max()) <= POSTNET_TOL
+    # vtts.py:106-107: output = mel_linear(dec); postnet_output = postnet(output) + output
+    out = v.mel_linear(torch.from_numpy(g["dec"]).to(dev), torch.from_numpy(g["lin_w"]), torch.from_numpy(g["lin_b"]))
+    assert float((out.cpu() - torch.from_numpy(g["mel"])).abs().max()) <= 1e-5
+    pm = pn(out, add_input=True).cpu()
+    assert float((pm - torch.from_numpy(g["postnet_mel"])).abs().max()) <= POSTNET_TOL
+
+
+@pytest.mark.gpu
+def test_postnet_against_oracle_config3_shape(dev):
+    """Batch 64 of ragged-length-like frames (config 3 feeds LengthRegulator output through decoder -> this tail)."""
+    from oracle import postnet_oracle as po
+    from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict
+    sd = seeded_postnet_state_dict(99)
+    pn = v.PostNet()
+    pn.load_state_dict(sd)
+    pn.eval().to(dev)
+    x = torch.randn(64, 490, 80, generator=torch.Generator().manual_seed(5)) * 2 - 3
+    ref = po.postnet_forward(sd, x)
+    got = pn(x.to(dev)).cpu()
+    assert float((got - ref).abs().max()) <= POSTNET_TOL
+    lin_w = torch.randn(80, 256, generator=torch.Generator().manual_seed(6)) / 16
+    dec = torch.randn(3, 33, 256, generator=torch.Generator().manual_seed(8))
+    assert float((v.mel_linear(dec.to(dev), lin_w).cpu() - dec @ lin_w.t()).abs().max()) <= 1e-5
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

@@ -101,3 +101,42 @@ def test_emulated_bf16_pipeline_is_inside_tolerance(golden_dir, sd1234):
     mel = torch.from_numpy(g["mel"])
     emu = generator_forward_emulated(sd1234, mel, mode="bf16", residual="fp32")
     assert snr_db(torch.from_numpy(g["wav"]), emu) > 40.0
+
+
+# ------------------------------------------------------------------------------------------
+# PostNet + mel_linear: the oracle against outputs of the reference classes
+# ------------------------------------------------------------------------------------------
+def test_postnet_oracle_matches_reference_golden(golden_dir):
+    import hashlib
+    from oracle import postnet_oracle as po
+    from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict
+    g = np.load(os.path.join(golden_dir, "postnet.npz"))
+    sd = seeded_postnet_state_dict(4321)
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        h.update(k.encode())
+        h.update(sd[k].contiguous().numpy().tobytes())
+    assert h.hexdigest().encode() == bytes(g["sd_sha256"]), "seeded PostNet weights drifted from the fixture"
+    for name in "abc":
+        y = po.postnet_forward(sd, torch.from_numpy(g[f"x_{name}"]))
+        assert float((y - torch.from_numpy(g[f"y_{name}"])).abs().max()) <= 1e-5
+    out, pm = po.vtts_tail(sd, torch.from_numpy(g["lin_w"]), torch.from_numpy(g["lin_b"]), torch.from_numpy(g["dec"]))
+    assert float((out - torch.from_numpy(g["mel"])).abs().max()) <= 1e-5
+    assert float((pm - torch.from_numpy(g["postnet_mel"])).abs().max()) <= 1e-5
+
+
+def test_postnet_dropin_has_the_reference_state_dict_keys():
+    import visual_onoma_to_wave_b200 as v
+    from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict
+    pn = v.PostNet()
+    sd = seeded_postnet_state_dict(4321)
+    assert set(pn.state_dict().keys()) == set(sd.keys())
+    pn.load_state_dict(sd)                      # strict
+    pn.eval()
+    with pytest.raises(RuntimeError):           # no CPU fallback
+        pn(torch.zeros(1, 4, 80))
+    pn.train()
+    with pytest.raises(RuntimeError):           # inference only
+        pn(torch.zeros(1, 4, 80))
+    blob = pn.folded_blob()
+    assert blob.numel() == 5 * (80 * 512 + 3 * 512 * 512 + 512 * 80) + 4 * 512 + 80

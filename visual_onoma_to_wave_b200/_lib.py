@@ -52,6 +52,13 @@ SYMBOLS = {
     "vo2w_generator_last_launches": (C.c_int, [C.c_void_p]),
     "vo2w_generator_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "vo2w_generator_get_timing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "vo2w_postnet_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "vo2w_postnet_destroy": (C.c_int, [C.c_void_p]),
+    "vo2w_postnet_workspace_bytes": (C.c_size_t, [C.c_void_p, C.c_int, C.c_int]),
+    "vo2w_postnet_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                       C.c_size_t, C.c_void_p]),
+    "vo2w_linear_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p,
+                                      C.c_void_p]),
     "vo2w_lr_lengths": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vo2w_length_regulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
                                        C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]),

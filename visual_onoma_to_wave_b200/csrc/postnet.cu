@@ -1,0 +1,184 @@
+// mel_linear + PostNet of the acoustic model's tail: the step between the mel decoder and
+// the vocoder.
+//
+//   PostNet.forward (scripts/transformer/Layers.py:126-137, eval mode): x [B,L,n_mel] -> transpose ->
+//       4 x tanh(BatchNorm1d(Conv1d k5)) -> BatchNorm1d(Conv1d k5) -> transpose      (dropout is the identity)
+//   vTTS.forward (scripts/model/vtts.py:106-107):  output = mel_linear(output); postnet_output = postnet(output) + output
+//
+// BatchNorm (eval) is an affine map per channel, folded into the convolution's weight and bias by the caller
+// (postnet.py), as weight_norm is for the vocoder.  fp32 CUDA-core path: the layers are 8.7 MFLOP per frame, 1.4 % of
+// the vocoder's 614 MFLOP, so they ride the exact-mode convolution kernel (conv_simt.cu) between two tiled
+// transposes; the second transpose fuses the `+ output` of vtts.py:107 on request.
+#include <vector>
+
+#include "conv_simt.cuh"
+
+struct vo2w_postnet {
+    int n_mel = 0, dim = 0, k = 0, n_conv = 0;
+    float* w_dev = nullptr;
+    std::vector<size_t> w_off, b_off;
+};
+
+namespace {
+
+// [B,R,C] -> [B,C,R] (32 x 32 tiles through shared memory); optional `add` [B,C,R] is added to the result
+__global__ void __launch_bounds__(256) transpose_add_kernel(const float* __restrict__ in, const float* __restrict__ add,
+                                                            float* __restrict__ out, int R, int C) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const float* ib = in + (size_t)b * R * C;
+    for (int i = ty; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + tx;
+        tile[i][tx] = (r < R && c < C) ? ib[(size_t)r * C + c] : 0.f;
+    }
+    __syncthreads();
+    float* ob = out + (size_t)b * R * C;
+    const float* ab = add ? add + (size_t)b * R * C : nullptr;
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + tx;
+        if (r < R && c < C) {
+            float v = tile[tx][i];
+            if (ab) v += ab[(size_t)c * R + r];
+            ob[(size_t)c * R + r] = v;
+        }
+    }
+}
+
+int transpose_add(const float* in, const float* add, float* out, int B, int R, int C, cudaStream_t st) {
+    dim3 grid((unsigned)vo2w_ceil_div(C, 32), (unsigned)vo2w_ceil_div(R, 32), (unsigned)B);
+    transpose_add_kernel<<<grid, 256, 0, st>>>(in, add, out, R, C);
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}
+
+// y[r, n] = sum_k x[r, k] * w[n, k] + b[n]   (nn.Linear on the last axis; rows = every leading axis flattened).
+// One CTA: 32 rows x all N outputs; x rows staged in shared memory, each warp owns 4 rows, lanes walk n.
+constexpr int LIN_ROWS = 32;
+__global__ void __launch_bounds__(256) linear_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                          const float* __restrict__ bias, float* __restrict__ y,
+                                                          long long rows, int K, int N) {
+    extern __shared__ float xs[];   // [LIN_ROWS][K]
+    const long long r0 = (long long)blockIdx.x * LIN_ROWS;
+    const int n_rows = (int)min((long long)LIN_ROWS, rows - r0);
+    for (int e = threadIdx.x; e < n_rows * K; e += 256) xs[e] = x[(size_t)r0 * K + e];
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int n = lane; n < N; n += 32) {
+        const float* wn = w + (size_t)n * K;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int kk = 0; kk < K; ++kk) {
+            const float wv = __ldg(wn + kk);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[i] = fmaf(xs[(warp * 4 + i) * K + kk], wv, acc[i]);
+        }
+        const float bv = bias ? __ldg(bias + n) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = warp * 4 + i;
+            if (r < n_rows) y[(size_t)(r0 + r) * N + n] = acc[i] + bv;
+        }
+    }
+}
+
+size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+}  // namespace
+
+extern "C" int vo2w_postnet_create(int n_mel, int dim, int k, int n_conv, const float* folded_host, size_t n_floats,
+                                   vo2w_postnet** out) {
+    VO2W_REQUIRE(folded_host && out, "postnet_create: null argument");
+    VO2W_REQUIRE(n_mel > 0 && dim > 0 && n_conv >= 2 && (k & 1) && k >= 1 && k <= 11, "postnet_create: bad shape (n_mel %d dim %d k %d n_conv %d)",
+                 n_mel, dim, k, n_conv);
+    int rc = vo2w_device_check();
+    if (rc != VO2W_OK) return rc;
+    vo2w_postnet* p = new vo2w_postnet();
+    p->n_mel = n_mel; p->dim = dim; p->k = k; p->n_conv = n_conv;
+    size_t off = 0;
+    for (int i = 0; i < n_conv; ++i) {
+        const int cin = i == 0 ? n_mel : dim, cout = i == n_conv - 1 ? n_mel : dim;
+        p->w_off.push_back(off);
+        off += (size_t)cout * cin * k;
+        p->b_off.push_back(off);
+        off += (size_t)cout;
+    }
+    if (off != n_floats) {
+        vo2w_set_error("postnet_create: weight blob has %zu floats, shape needs %zu", n_floats, off);
+        delete p;
+        return VO2W_E_INVALID;
+    }
+    if (cudaMalloc(&p->w_dev, n_floats * 4) != cudaSuccess ||
+        cudaMemcpy(p->w_dev, folded_host, n_floats * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+        vo2w_set_error("postnet_create: uploading weights failed");
+        if (p->w_dev) cudaFree(p->w_dev);
+        delete p;
+        return VO2W_E_CUDA;
+    }
+    *out = p;
+    return VO2W_OK;
+}
+
+extern "C" int vo2w_postnet_destroy(vo2w_postnet* p) {
+    if (!p) return VO2W_OK;
+    if (p->w_dev) cudaFree(p->w_dev);
+    delete p;
+    return VO2W_OK;
+}
+
+extern "C" size_t vo2w_postnet_workspace_bytes(const vo2w_postnet* p, int B, int L) {
+    if (!p || B <= 0 || L <= 0) return 0;
+    return align256((size_t)B * p->n_mel * L * 4) + 2 * align256((size_t)B * p->dim * L * 4);
+}
+
+extern "C" int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int L, float* out, int add_input,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
+    VO2W_REQUIRE(p && x && out, "postnet_forward: null argument");
+    VO2W_REQUIRE(B > 0 && L > 0 && B <= 65535, "postnet_forward: bad batch (B=%d L=%d)", B, L);
+    const size_t need = vo2w_postnet_workspace_bytes(p, B, L);
+    if (!workspace || workspace_bytes < need) {
+        vo2w_set_error("postnet_forward: workspace %zu bytes, need %zu", workspace_bytes, need);
+        return VO2W_E_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t* ws = (uint8_t*)workspace;
+    float* x_ncl = (float*)ws;
+    float* buf[2] = {(float*)(ws + align256((size_t)B * p->n_mel * L * 4)),
+                     (float*)(ws + align256((size_t)B * p->n_mel * L * 4) + align256((size_t)B * p->dim * L * 4))};
+    // x.contiguous().transpose(1, 2): [B,L,n_mel] -> [B,n_mel,L]
+    int rc = transpose_add(x, nullptr, x_ncl, B, L, p->n_mel, st);
+    if (rc != VO2W_OK) return rc;
+    const float* cur = x_ncl;
+    for (int i = 0; i < p->n_conv; ++i) {
+        const bool last = i == p->n_conv - 1;
+        SimtConv q;
+        memset(&q, 0, sizeof(q));
+        q.x = cur; q.w = p->w_dev + p->w_off[i]; q.bias = p->w_dev + p->b_off[i];
+        q.out = last ? buf[i & 1] : buf[i & 1];
+        q.B = B; q.Cin = i == 0 ? p->n_mel : p->dim; q.Cout = last ? p->n_mel : p->dim;
+        q.L = L; q.k = p->k; q.dil = 1; q.pad = (p->k - 1) / 2; q.stride = 1;
+        q.in_slope = 1.f; q.div = 1.f;
+        q.tanh_out = last ? 0 : 1;          // torch.tanh on all but the last convolution (Layers.py:129-131)
+        rc = simt_conv1d(q, st);
+        if (rc != VO2W_OK) return rc;
+        cur = q.out;
+    }
+    // transpose back; `+ output` of vtts.py:107 fused on request (the addend is the time-major input itself)
+    return transpose_add(cur, add_input ? x : nullptr, out, B, p->n_mel, L, st);
+}
+
+extern "C" int vo2w_linear_forward(const float* x, const float* w, const float* bias, long long rows, int K, int N, float* y,
+                                   void* stream) {
+    VO2W_REQUIRE(x && w && y, "linear_forward: null argument");
+    VO2W_REQUIRE(rows > 0 && K > 0 && N > 0 && (size_t)LIN_ROWS * K * 4 <= 96 * 1024, "linear_forward: bad shape (rows %lld K %d N %d)",
+                 rows, K, N);
+    static bool attr_set = false;
+    if (!attr_set) {
+        VO2W_CUDA_OK(cudaFuncSetAttribute(linear_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_set = true;
+    }
+    const long long blocks = (rows + LIN_ROWS - 1) / LIN_ROWS;
+    VO2W_REQUIRE(blocks <= 0x7fffffffLL, "linear_forward: too many rows");
+    linear_rows_kernel<<<(unsigned)blocks, 256, (size_t)LIN_ROWS * K * 4, (cudaStream_t)stream>>>(x, w, bias, y, rows, K, N);
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}

@@ -77,3 +77,21 @@ def synthetic_durations(B: int, T_src: int, seed: int = 0, hi: int = 25) -> torc
     """int64 [B,T_src] ~ U{0..hi-1} (config 3)."""
     gen = torch.Generator().manual_seed(seed)
     return torch.randint(0, hi, (B, T_src), generator=gen)
+
+
+def seeded_postnet_state_dict(seed: int = 4321, n_mel: int = 80, dim: int = 512, k: int = 5, n_conv: int = 5):
+    """State dict with the reference PostNet's keys (scripts/transformer/Layers.py:67-124): seeded convolution
+    weights and NON-trivial BatchNorm statistics, so that the eval-mode fold is actually exercised."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    chans = [n_mel] + [dim] * (n_conv - 1) + [n_mel]
+    for i in range(n_conv):
+        cin, cout = chans[i], chans[i + 1]
+        sd[f"convolutions.{i}.0.conv.weight"] = torch.randn(cout, cin, k, generator=g) * (1.5 / (cin * k) ** 0.5)
+        sd[f"convolutions.{i}.0.conv.bias"] = torch.randn(cout, generator=g) * 0.1
+        sd[f"convolutions.{i}.1.weight"] = torch.rand(cout, generator=g) + 0.5
+        sd[f"convolutions.{i}.1.bias"] = torch.randn(cout, generator=g) * 0.1
+        sd[f"convolutions.{i}.1.running_mean"] = torch.randn(cout, generator=g) * 0.2
+        sd[f"convolutions.{i}.1.running_var"] = torch.rand(cout, generator=g) + 0.5
+        sd[f"convolutions.{i}.1.num_batches_tracked"] = torch.tensor(100)
+    return sd
