@@ -170,6 +170,25 @@ int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int L, float* o
 int vo2w_linear_forward(const float* x, const float* w, const float* bias, long long rows, int K, int N,
                         float* y, void* stream);
 
+/* ---- mel Decoder: the FFT-block stack ----------------------------
+ * Replaces Decoder.forward (scripts/transformer/Models.py:168-197) in eval mode:
+ *   dec = x + pos[:L];  per layer FFTBlock.forward (scripts/transformer/Layers.py:21-30) =
+ *   MultiHeadAttention (SubLayers.py:31-62; key padding mask, softmax(q k^T / sqrt(d_k)) v, LayerNorm(fc + x)),
+ *   masked_fill(mask, 0), PositionwiseFeedForward (SubLayers.py:95-104; LayerNorm(w_2(relu(w_1 x)) + x)),
+ *   masked_fill(mask, 0).
+ * x, out [B,L,d_model] fp32; pos [L,d_model] = the first L rows of the sinusoid table (position_enc, or a longer
+ * table built the same way when L > max_seq_len, Models.py:175-181); mask [B,L] bytes, 1 = padding frame, or NULL.
+ * Head size d_model / n_head must be 128 (the reference's 256 / 2).  `blob_host`, per layer: [w_qs|w_ks|w_vs]
+ * [3D,D], their biases [3D], fc [D,D], bias, attention LayerNorm gamma, beta, w_1 [d_inner,D,k1], bias,
+ * w_2 [D,d_inner,k2], bias, feed-forward LayerNorm gamma, beta.  fp32 CUDA-core path. */
+typedef struct vo2w_decoder vo2w_decoder;
+int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1, int k2, int n_layers, const float* blob_host,
+                        size_t n_floats, vo2w_decoder** out);
+int vo2w_decoder_destroy(vo2w_decoder* d);
+size_t vo2w_decoder_workspace_bytes(const vo2w_decoder* d, int B, int L);
+int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float* pos, const uint8_t* mask, int B, int L,
+                         float* out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad
  * (scripts/utils/tools.py:669-687).

@@ -166,6 +166,36 @@ def postnet_golden():
     print("postnet.npz written")
 
 
+def decoder_golden():
+    """mel Decoder FFT-block stack, outputs of the reference's own class."""
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
+    for m in ("utils.symbols", "model.visual_feature_extractor"):    # Encoder-only imports of Models.py (not on this path)
+        sys.modules.setdefault(m, MagicMock())
+    from transformer.Models import Decoder    # reference
+    out = {}
+    g = torch.Generator().manual_seed(11)
+    cases = {  # name: (config kwargs, seed, B, L, lengths)
+        "full": (dict(), 2468, 2, 61, [61, 40]),                                   # the shipped model.yaml shape
+        "small": (dict(n_layers=2, d_inner=256, kernels=(3, 1)), 97, 3, 70, [70, 1, 33]),
+        "long": (dict(n_layers=1, d_inner=128, kernels=(9, 1), max_seq_len=32), 98, 2, 50, [50, 45]),   # L > max_seq_len
+    }
+    with torch.no_grad():
+        for name, (kw, seed, B, L, lens) in cases.items():
+            sd = seeded_decoder_state_dict(seed, **kw)
+            dec = Decoder(decoder_config(**kw))
+            dec.load_state_dict(sd)             # strict: the key set is the reference's
+            dec.eval()
+            x = torch.randn(B, L, 256, generator=g)
+            mask = torch.arange(L)[None, :] >= torch.tensor(lens)[:, None]
+            y, m2 = dec(x, mask)
+            assert torch.equal(m2, mask)
+            out[f"sha_{name}"] = np.frombuffer(sd_sha256(sd).encode(), dtype=np.uint8)
+            out[f"x_{name}"], out[f"mask_{name}"], out[f"y_{name}"] = x.numpy(), mask.numpy(), y.numpy()
+    np.savez_compressed(os.path.join(HERE, "decoder.npz"), **out)
+    print("decoder.npz written")
+
+
 if __name__ == "__main__":
     main()
     postnet_golden()
+    decoder_golden()

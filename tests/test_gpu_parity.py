@@ -359,6 +359,56 @@ def test_postnet_against_oracle_config3_shape(dev):
     assert float((v.mel_linear(dec.to(dev), lin_w).cpu() - dec @ lin_w.t()).abs().max()) <= 1e-5
 
 
+DECODER_TOL = 1e-4   # fp32 path, max-abs on LayerNorm-scaled activations (same gate as the waveform's fp32 mode)
+DECODER_CASES = {"full": (dict(), 2468), "small": (dict(n_layers=2, d_inner=256, kernels=(3, 1)), 97),
+                 "long": (dict(n_layers=1, d_inner=128, kernels=(9, 1), max_seq_len=32), 98)}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(DECODER_CASES))
+def test_decoder_against_reference_golden(dev, golden_dir, name):
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
+    g = np.load(os.path.join(golden_dir, "decoder.npz"))
+    kw, seed = DECODER_CASES[name]
+    dec = v.Decoder(decoder_config(**kw))
+    dec.load_state_dict(seeded_decoder_state_dict(seed, **kw))
+    dec.eval().to(dev)
+    mask = torch.from_numpy(g[f"mask_{name}"])
+    y, m2 = dec(torch.from_numpy(g[f"x_{name}"]).to(dev), mask.to(dev))
+    assert torch.equal(m2.cpu(), mask)
+    ref = torch.from_numpy(g[f"y_{name}"])
+    assert y.shape == ref.shape
+    assert float((y.cpu() - ref).abs().max()) <= DECODER_TOL
+    assert float(y.cpu()[mask].abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+def test_decoder_against_oracle_ragged_batch(dev):
+    """LengthRegulator-shaped input: ragged lengths, several key tiles, lengths that are not tile multiples."""
+    from oracle import decoder_oracle as do
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
+    kw = dict(n_layers=2)
+    sd = seeded_decoder_state_dict(5, **kw)
+    dec = v.Decoder(decoder_config(**kw))
+    dec.load_state_dict(sd)
+    dec.eval().to(dev)
+    lens = torch.tensor([490, 257, 64, 65, 1, 128, 300, 33])
+    L = int(lens.max())
+    x = torch.randn(len(lens), L, 256, generator=torch.Generator().manual_seed(3))
+    mask = torch.arange(L)[None, :] >= lens[:, None]
+    ref, _ = do.decoder_forward(sd, x, mask)
+    got, _ = dec(x.to(dev), mask.to(dev))
+    assert float((got.cpu() - ref).abs().max()) <= DECODER_TOL
+    # LengthRegulator -> Decoder, the order of vTTS.forward (scripts/model/vtts.py:95-105)
+    dur = torch.randint(0, 6, (3, 40), generator=torch.Generator().manual_seed(4))
+    h = torch.randn(3, 40, 256, generator=torch.Generator().manual_seed(6))
+    out, mel_len = v.LengthRegulator()(h.to(dev), dur.to(dev), None)
+    m = torch.arange(out.shape[1], device=dev)[None, :] >= mel_len[:, None]
+    got, _ = dec(out, m)
+    ref, _ = do.decoder_forward(sd, out.cpu(), m.cpu())
+    assert float((got.cpu() - ref).abs().max()) <= DECODER_TOL
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

@@ -140,3 +140,60 @@ def test_postnet_dropin_has_the_reference_state_dict_keys():
         pn(torch.zeros(1, 4, 80))
     blob = pn.folded_blob()
     assert blob.numel() == 5 * (80 * 512 + 3 * 512 * 512 + 512 * 80) + 4 * 512 + 80
+
+
+# ------------------------------------------------------------------------------------------
+# mel Decoder FFT-block stack: the oracle against outputs of the reference class
+# ------------------------------------------------------------------------------------------
+DECODER_CASES = {"full": (dict(), 2468), "small": (dict(n_layers=2, d_inner=256, kernels=(3, 1)), 97),
+                 "long": (dict(n_layers=1, d_inner=128, kernels=(9, 1), max_seq_len=32), 98)}
+
+
+def _sha(sd):
+    import hashlib
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        h.update(k.encode())
+        h.update(sd[k].contiguous().numpy().tobytes())
+    return h.hexdigest().encode()
+
+
+@pytest.mark.parametrize("name", list(DECODER_CASES))
+def test_decoder_oracle_matches_reference_golden(golden_dir, name):
+    from oracle import decoder_oracle as do
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict
+    g = np.load(os.path.join(golden_dir, "decoder.npz"))
+    kw, seed = DECODER_CASES[name]
+    sd = seeded_decoder_state_dict(seed, **kw)
+    assert _sha(sd) == bytes(g[f"sha_{name}"]), "seeded Decoder weights drifted from the fixture"
+    mask = torch.from_numpy(g[f"mask_{name}"])
+    y, m2 = do.decoder_forward(sd, torch.from_numpy(g[f"x_{name}"]), mask)
+    assert torch.equal(m2, mask)
+    ref = torch.from_numpy(g[f"y_{name}"])
+    assert float((y - ref).abs().max()) <= 2e-5
+    assert float(y[mask].abs().max()) == 0.0          # padding frames are zeroed after every sub-layer
+
+
+def test_sinusoid_table_matches_the_reference_formula():
+    from oracle.decoder_oracle import sinusoid_table as slow
+    from visual_onoma_to_wave_b200.synthetic import sinusoid_table as fast
+    assert torch.equal(slow(67, 256), fast(67, 256))
+
+
+def test_decoder_dropin_has_the_reference_state_dict_keys():
+    import visual_onoma_to_wave_b200 as v
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
+    kw = dict(n_layers=2, d_inner=256, kernels=(3, 1))
+    dec = v.Decoder(decoder_config(**kw))
+    sd = seeded_decoder_state_dict(97, **kw)
+    assert set(dec.state_dict().keys()) == set(sd.keys())
+    dec.load_state_dict(sd)                     # strict
+    dec.eval()
+    mask = torch.zeros(1, 4, dtype=torch.bool)
+    with pytest.raises(RuntimeError):           # no CPU fallback
+        dec(torch.zeros(1, 4, 256), mask)
+    dec.train()
+    with pytest.raises(RuntimeError):           # inference only
+        dec(torch.zeros(1, 4, 256), mask)
+    D, H = 256, 256
+    assert dec.weight_blob().numel() == 2 * (4 * D * D + 4 * D + 4 * D + H * D * 3 + H + D * H + D)

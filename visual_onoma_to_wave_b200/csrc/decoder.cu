@@ -1,0 +1,319 @@
+// FFT-block stack of the mel decoder: the step LengthRegulator feeds.
+//
+//   Decoder.forward (scripts/transformer/Models.py:168-197, eval):  x + sinusoid position table, then per layer
+//   FFTBlock.forward (scripts/transformer/Layers.py:21-30):
+//       MultiHeadAttention (SubLayers.py:31-62): q,k,v = Linear(x); softmax(q k^T / sqrt(d_k), key mask) v;
+//                                                LayerNorm(fc(.) + x);            masked_fill(mask, 0)
+//       PositionwiseFeedForward (SubLayers.py:95-104): LayerNorm(w_2(relu(w_1(x^T)))^T + x);  masked_fill(mask, 0)
+//   (dropout is the identity in eval mode).
+//
+// fp32 CUDA-core path.  The stack runs channel-major ([B,D,L], one tiled transpose in and one out): every Linear is
+// a k=1 convolution on the exact-mode convolution kernel (conv_simt.cu, q|k|v fused into one [3D,D] layer, the fc
+// and w_2 layers fuse their residual add), attention is a tiled online-softmax kernel (64 queries x 64 keys per
+// step, d_k = 128), LayerNorm + padding mask one kernel over the channel axis.
+#include <vector>
+
+#include "conv_simt.cuh"
+#include "rows.cuh"
+
+namespace {
+
+constexpr int AQ = 64, AK = 64, AD = 128;          // queries / keys per tile, head size
+constexpr int AQS = AD + 1, APS = AK + 1;           // padded shared-memory strides
+constexpr size_t ATTN_SMEM = ((size_t)AQ * AQS + (size_t)AK * AQS + (size_t)AQ * APS + 3 * AQ) * 4;
+
+// out[b, q, h*128 + :] = softmax_k(q_h . k_h / sqrt(128) masked) v_h   for one (query tile, head, utterance)
+// qkv [B][3*D][L] (q | k | v channels, head h at channels h*128), mask [B][L] (1 = padding key) or null, out [B][D][L]
+__global__ void __launch_bounds__(256) attention_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ mask,
+                                                        float* __restrict__ out, int L, int D, float scale) {
+    extern __shared__ float sm[];
+    float* Qs = sm;                       // [AQ][AQS]
+    float* KVs = Qs + AQ * AQS;           // [AK][AQS]   keys, then values
+    float* Ps = KVs + AK * AQS;           // [AQ][APS]   scores, then probabilities
+    float* rowM = Ps + AQ * APS;          // running max, running sum, rescale factor per query row
+    float* rowL = rowM + AQ;
+    float* rowA = rowL + AQ;
+    const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * AQ;
+    const int tid = threadIdx.x, tq = tid >> 4, tk = tid & 15, warp = tid >> 5, lane = tid & 31;
+    const float* base = qkv + ((size_t)b * 3 * D + (size_t)h * AD) * L;      // element (channel d, time t) at base[d * L + t]
+    const uint8_t* mb = mask ? mask + (size_t)b * L : nullptr;
+
+    for (int e = tid; e < AQ * AD; e += 256) {
+        const int d = e >> 6, r = e & 63;                       // time fastest: coalesced
+        Qs[r * AQS + d] = (q0 + r < L) ? base[(size_t)d * L + q0 + r] * scale : 0.f;
+    }
+    if (tid < AQ) { rowM[tid] = -1e30f; rowL[tid] = 0.f; rowA[tid] = 0.f; }
+    float O[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) O[i][e] = 0.f;
+    __syncthreads();
+
+    for (int k0 = 0; k0 < L; k0 += AK) {
+        for (int e = tid; e < AK * AD; e += 256) {
+            const int d = e >> 6, r = e & 63;
+            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(D + d) * L + k0 + r] : 0.f;
+        }
+        __syncthreads();
+        float S[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) S[i][j] = 0.f;
+        for (int d = 0; d < AD; ++d) {
+            float qv[4], kv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) qv[i] = Qs[(tq * 4 + i) * AQS + d];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) kv[j] = KVs[(tk * 4 + j) * AQS + d];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) S[i][j] = fmaf(qv[i], kv[j], S[i][j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int kk = k0 + tk * 4 + j;
+            const bool dead = kk >= L || (mb && mb[kk]);          // masked_fill(mask, -inf) before the softmax
+#pragma unroll
+            for (int i = 0; i < 4; ++i) Ps[(tq * 4 + i) * APS + tk * 4 + j] = dead ? -1e30f : S[i][j];
+        }
+        __syncthreads();
+        // online softmax: warp w owns rows 8w .. 8w+7, lanes walk the 64 keys
+        for (int r = warp * 8; r < warp * 8 + 8; ++r) {
+            const float s0 = Ps[r * APS + lane], s1 = Ps[r * APS + lane + 32];
+            float mx = fmaxf(s0, s1);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            const float m_old = rowM[r], m_new = fmaxf(m_old, mx);
+            const float p0 = s0 <= -1e30f ? 0.f : expf(s0 - m_new), p1 = s1 <= -1e30f ? 0.f : expf(s1 - m_new);
+            float sum = p0 + p1;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            Ps[r * APS + lane] = p0;
+            Ps[r * APS + lane + 32] = p1;
+            if (lane == 0) {
+                const float a = expf(m_old - m_new);
+                rowA[r] = a;
+                rowL[r] = rowL[r] * a + sum;
+                rowM[r] = m_new;
+            }
+        }
+        __syncthreads();
+        for (int e = tid; e < AK * AD; e += 256) {                  // values over the keys
+            const int d = e >> 6, r = e & 63;
+            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(2 * D + d) * L + k0 + r] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float a = rowA[tq * 4 + i];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) O[i][e] *= a;
+        }
+        for (int k = 0; k < AK; ++k) {
+            float pv[4], vv[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) pv[i] = Ps[(tq * 4 + i) * APS + k];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) vv[e] = KVs[k * AQS + tk + 16 * e];      // column tk + 16 e: conflict-free
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) O[i][e] = fmaf(pv[i], vv[e], O[i][e]);
+        }
+        __syncthreads();
+    }
+    // through shared memory (the query tile is dead) so that the channel-major store is coalesced along time
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float inv = 1.f / rowL[tq * 4 + i];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) Qs[(tq * 4 + i) * AQS + tk + 16 * e] = O[i][e] * inv;
+    }
+    __syncthreads();
+    float* ob = out + ((size_t)b * D + (size_t)h * AD) * L;
+    for (int e = tid; e < AQ * AD; e += 256) {
+        const int d = e >> 6, r = e & 63;
+        if (q0 + r < L) ob[(size_t)d * L + q0 + r] = Qs[r * AQS + d];
+    }
+}
+
+// y[b,:,l] = mask[b,l] ? 0 : LayerNorm_over_channels(x[b,:,l]) * gamma + beta   (eps 1e-5, biased variance;
+// nn.LayerNorm(d_model) on the time-major view, then masked_fill(mask.unsqueeze(-1), 0): SubLayers.py:60,103, Layers.py:24-28)
+// block = 32 time steps x 8 channel groups
+__global__ void __launch_bounds__(256) layernorm_ncl_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, const uint8_t* __restrict__ mask,
+                                                            float* __restrict__ y, int D, int L) {
+    __shared__ float red[8][33];
+    const int b = blockIdx.y, l = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5, tl = threadIdx.x & 31;
+    const bool live = l < L;
+    const float* xb = x + (size_t)b * D * L;
+    float* yb = y + (size_t)b * D * L;
+    float sum = 0.f;
+    if (live) for (int c = g; c < D; c += 8) sum += xb[(size_t)c * L + l];
+    red[g][tl] = sum;
+    __syncthreads();
+    float mean = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mean += red[i][tl];
+    mean *= 1.0f / D;
+    __syncthreads();
+    float sq = 0.f;
+    if (live) for (int c = g; c < D; c += 8) { const float d = xb[(size_t)c * L + l] - mean; sq = fmaf(d, d, sq); }
+    red[g][tl] = sq;
+    __syncthreads();
+    float var = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) var += red[i][tl];
+    const float rstd = rsqrtf(var * (1.0f / D) + 1e-5f);
+    if (!live) return;
+    const bool dead = mask && mask[(size_t)b * L + l];
+    for (int c = g; c < D; c += 8)
+        yb[(size_t)c * L + l] = dead ? 0.f : (xb[(size_t)c * L + l] - mean) * rstd * gamma[c] + beta[c];
+}
+
+}  // namespace
+
+int ncl_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, int B, int D, int L,
+                       cudaStream_t st) {
+    dim3 grid((unsigned)vo2w_ceil_div(L, 32), (unsigned)B);
+    layernorm_ncl_kernel<<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, D, L);
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}
+
+int ncl_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st) {
+    VO2W_REQUIRE(D == n_head * AD, "attention: head size must be %d (d_model %d, heads %d)", AD, D, n_head);
+    static bool attr_set = false;
+    if (!attr_set) {
+        VO2W_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATTN_SMEM));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)vo2w_ceil_div(L, AQ), (unsigned)n_head, (unsigned)B);
+    attention_kernel<<<grid, 256, ATTN_SMEM, st>>>(qkv, mask, out, L, D, 1.0f / sqrtf((float)AD));
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// handle: the layer stack's parameters in one device blob
+// ---------------------------------------------------------------------------------------------------------------
+struct vo2w_decoder {
+    int d_model = 0, n_head = 0, d_inner = 0, k1 = 0, k2 = 0, n_layers = 0;
+    float* w_dev = nullptr;
+    struct Layer { size_t wqkv, bqkv, wfc, bfc, ln1g, ln1b, w1, b1, w2, b2, ln2g, ln2b; };
+    std::vector<Layer> layers;
+};
+
+namespace {
+
+size_t dec_align(size_t v) { return (v + 255) / 256 * 256; }
+
+int k1conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int Cin, int Cout, int L,
+           int k, float in_slope, cudaStream_t st) {
+    SimtConv q;
+    memset(&q, 0, sizeof(q));
+    q.x = x; q.w = w; q.bias = bias; q.res = res; q.out = out;
+    q.B = B; q.Cin = Cin; q.Cout = Cout; q.L = L; q.k = k; q.dil = 1; q.pad = (k - 1) / 2; q.stride = 1;
+    q.in_slope = in_slope; q.div = 1.f;
+    return simt_conv1d(q, st);
+}
+
+}  // namespace
+
+// blob, per layer: [w_qs | w_ks | w_vs] [3D,D], their biases [3D], fc [D,D] + bias, attention LayerNorm gamma, beta,
+// w_1 [d_inner,D,k1] + bias, w_2 [D,d_inner,k2] + bias, feed-forward LayerNorm gamma, beta
+extern "C" int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1, int k2, int n_layers, const float* blob_host,
+                                   size_t n_floats, vo2w_decoder** out) {
+    VO2W_REQUIRE(blob_host && out, "decoder_create: null argument");
+    VO2W_REQUIRE(d_model > 0 && n_head > 0 && d_model == n_head * AD, "decoder_create: d_model %d / heads %d: head size must be %d",
+                 d_model, n_head, AD);
+    VO2W_REQUIRE(d_inner > 0 && n_layers > 0 && (k1 & 1) && (k2 & 1) && k1 >= 1 && k1 <= 11 && k2 >= 1 && k2 <= 11,
+                 "decoder_create: bad shape (d_inner %d, kernels %d/%d, layers %d)", d_inner, k1, k2, n_layers);
+    int rc = vo2w_device_check();
+    if (rc != VO2W_OK) return rc;
+    vo2w_decoder* d = new vo2w_decoder();
+    d->d_model = d_model; d->n_head = n_head; d->d_inner = d_inner; d->k1 = k1; d->k2 = k2; d->n_layers = n_layers;
+    const size_t D = (size_t)d_model, H = (size_t)d_inner;
+    size_t off = 0;
+    auto take = [&](size_t n) { const size_t o = off; off += n; return o; };
+    for (int i = 0; i < n_layers; ++i) {
+        vo2w_decoder::Layer l;
+        l.wqkv = take(3 * D * D); l.bqkv = take(3 * D);
+        l.wfc = take(D * D); l.bfc = take(D);
+        l.ln1g = take(D); l.ln1b = take(D);
+        l.w1 = take(H * D * k1); l.b1 = take(H);
+        l.w2 = take(D * H * k2); l.b2 = take(D);
+        l.ln2g = take(D); l.ln2b = take(D);
+        d->layers.push_back(l);
+    }
+    if (off != n_floats) {
+        vo2w_set_error("decoder_create: weight blob has %zu floats, shape needs %zu", n_floats, off);
+        delete d;
+        return VO2W_E_INVALID;
+    }
+    if (cudaMalloc(&d->w_dev, n_floats * 4) != cudaSuccess ||
+        cudaMemcpy(d->w_dev, blob_host, n_floats * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+        vo2w_set_error("decoder_create: uploading weights failed");
+        if (d->w_dev) cudaFree(d->w_dev);
+        delete d;
+        return VO2W_E_CUDA;
+    }
+    *out = d;
+    return VO2W_OK;
+}
+
+extern "C" int vo2w_decoder_destroy(vo2w_decoder* d) {
+    if (!d) return VO2W_OK;
+    if (d->w_dev) cudaFree(d->w_dev);
+    delete d;
+    return VO2W_OK;
+}
+
+extern "C" size_t vo2w_decoder_workspace_bytes(const vo2w_decoder* d, int B, int L) {
+    if (!d || B <= 0 || L <= 0) return 0;
+    const size_t bl = (size_t)B * L * 4;
+    return 2 * dec_align(bl * d->d_model) + dec_align(bl * 3 * d->d_model) + dec_align(bl * d->d_inner);
+}
+
+// x [B,L,D] time-major, pos [L,D] (the sinusoid table's first L rows), mask [B,L] bytes (1 = padding) or null,
+// out [B,L,D]
+extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float* pos, const uint8_t* mask, int B, int L,
+                                    float* out, void* workspace, size_t workspace_bytes, void* stream) {
+    VO2W_REQUIRE(d && x && pos && out, "decoder_forward: null argument");
+    VO2W_REQUIRE(B > 0 && L > 0 && B <= 65535, "decoder_forward: bad batch (B=%d L=%d)", B, L);
+    const size_t need = vo2w_decoder_workspace_bytes(d, B, L);
+    if (!workspace || workspace_bytes < need) {
+        vo2w_set_error("decoder_forward: workspace %zu bytes, need %zu", workspace_bytes, need);
+        return VO2W_E_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int D = d->d_model, H = d->d_inner;
+    const size_t bl = (size_t)B * L * 4;
+    uint8_t* ws = (uint8_t*)workspace;
+    float* cur = (float*)ws;                                   // [B,D,L] layer input / output
+    float* tmp = (float*)(ws + dec_align(bl * D));             // [B,D,L] pre-LayerNorm sums
+    float* qkv = (float*)(ws + 2 * dec_align(bl * D));         // [B,3D,L]
+    float* hid = (float*)(ws + 2 * dec_align(bl * D) + dec_align(bl * 3 * D));   // [B,d_inner,L]; first holds the attention output
+
+    // enc_seq + position_enc[:, :L]  (Models.py:184-186), then channel-major for the whole stack
+    int rc = rows_add_table(x, pos, tmp, B, L, D, st);
+    if (rc != VO2W_OK) return rc;
+    rc = rows_transpose_add(tmp, nullptr, cur, B, L, D, st);
+    if (rc != VO2W_OK) return rc;
+    const float* W = d->w_dev;
+    for (const auto& l : d->layers) {
+        // MultiHeadAttention (SubLayers.py:31-62)
+        if ((rc = k1conv(cur, W + l.wqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 1.f, st)) != VO2W_OK) return rc;
+        if ((rc = ncl_attention(qkv, mask, hid, B, L, D, d->n_head, st)) != VO2W_OK) return rc;
+        if ((rc = k1conv(hid, W + l.wfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 1.f, st)) != VO2W_OK) return rc;
+        if ((rc = ncl_layernorm_mask(tmp, W + l.ln1g, W + l.ln1b, mask, cur, B, D, L, st)) != VO2W_OK) return rc;
+        // PositionwiseFeedForward (SubLayers.py:95-104); relu rides the second convolution's staging (slope 0)
+        if ((rc = k1conv(cur, W + l.w1, W + l.b1, nullptr, hid, B, D, H, L, d->k1, 1.f, st)) != VO2W_OK) return rc;
+        if ((rc = k1conv(hid, W + l.w2, W + l.b2, cur, tmp, B, H, D, L, d->k2, 0.f, st)) != VO2W_OK) return rc;
+        if ((rc = ncl_layernorm_mask(tmp, W + l.ln2g, W + l.ln2b, mask, cur, B, D, L, st)) != VO2W_OK) return rc;
+    }
+    return rows_transpose_add(cur, nullptr, out, B, D, L, st);
+}

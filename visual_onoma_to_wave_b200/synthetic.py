@@ -95,3 +95,45 @@ def seeded_postnet_state_dict(seed: int = 4321, n_mel: int = 80, dim: int = 512,
         sd[f"convolutions.{i}.1.running_var"] = torch.rand(cout, generator=g) + 0.5
         sd[f"convolutions.{i}.1.num_batches_tracked"] = torch.tensor(100)
     return sd
+
+
+def sinusoid_table(n_position: int, d_hid: int) -> torch.Tensor:
+    """The reference's position table (scripts/transformer/Models.py:13-33): float64 angles
+    pos / 10000^(2 (j // 2) / d_hid), sin on even columns, cos on odd ones, cast to float32."""
+    import numpy as np
+    pos = np.arange(n_position, dtype=np.float64)[:, None]
+    j = np.arange(d_hid)[None, :]
+    table = pos / np.power(10000, 2 * (j // 2) / d_hid)
+    table[:, 0::2] = np.sin(table[:, 0::2])
+    table[:, 1::2] = np.cos(table[:, 1::2])
+    return torch.FloatTensor(table)
+
+
+def seeded_decoder_state_dict(seed: int = 2468, d_model: int = 256, n_head: int = 2, d_inner: int = 1024, kernels=(9, 1),
+                              n_layers: int = 6, max_seq_len: int = 1000):
+    """State dict with the reference Decoder's keys (scripts/transformer/Models.py:137-166, SubLayers.py): seeded
+    Linear / Conv1d weights and NON-trivial LayerNorm affine parameters."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {"position_enc": sinusoid_table(max_seq_len + 1, d_model).unsqueeze(0)}
+    for i in range(n_layers):
+        a, f = f"layer_stack.{i}.slf_attn.", f"layer_stack.{i}.pos_ffn."
+        for name in ("w_qs", "w_ks", "w_vs", "fc"):
+            sd[a + name + ".weight"] = torch.randn(d_model, d_model, generator=g) * (1.2 / d_model ** 0.5)
+            sd[a + name + ".bias"] = torch.randn(d_model, generator=g) * 0.1
+        sd[a + "layer_norm.weight"] = torch.rand(d_model, generator=g) + 0.5
+        sd[a + "layer_norm.bias"] = torch.randn(d_model, generator=g) * 0.1
+        sd[f + "w_1.weight"] = torch.randn(d_inner, d_model, kernels[0], generator=g) * (1.4 / (d_model * kernels[0]) ** 0.5)
+        sd[f + "w_1.bias"] = torch.randn(d_inner, generator=g) * 0.1
+        sd[f + "w_2.weight"] = torch.randn(d_model, d_inner, kernels[1], generator=g) * (1.4 / (d_inner * kernels[1]) ** 0.5)
+        sd[f + "w_2.bias"] = torch.randn(d_model, generator=g) * 0.1
+        sd[f + "layer_norm.weight"] = torch.rand(d_model, generator=g) + 0.5
+        sd[f + "layer_norm.bias"] = torch.randn(d_model, generator=g) * 0.1
+    return sd
+
+
+def decoder_config(d_model: int = 256, n_head: int = 2, d_inner: int = 1024, kernels=(9, 1), n_layers: int = 6,
+                   max_seq_len: int = 1000):
+    """The slice of config/*/model.yaml Decoder.__init__ reads (Models.py:140-154)."""
+    return {"max_seq_len": max_seq_len,
+            "transformer": {"decoder_hidden": d_model, "decoder_layer": n_layers, "decoder_head": n_head,
+                            "conv_filter_size": d_inner, "conv_kernel_size": list(kernels), "decoder_dropout": 0.2}}
