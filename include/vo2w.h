@@ -189,6 +189,30 @@ size_t vo2w_decoder_workspace_bytes(const vo2w_decoder* d, int B, int L);
 int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float* pos, const uint8_t* mask, int B, int L,
                          float* out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- VarianceAdaptor pieces in front of LengthRegulator -----------
+ * vo2w_varpred_*: replaces VariancePredictor.forward (scripts/model/modules.py:161-213) in eval mode:
+ *   x [B,T,d_in] fp32 -> LayerNorm(relu(Conv1d k3)) x 2 -> Linear(F,1).squeeze(-1) -> masked_fill(mask, 0) -> out [B,T].
+ *   mask [B,T] bytes (1 = padding token) or NULL.  kernel_size must be 3 (the reference pads the second convolution
+ *   by 1 whatever the kernel size, modules.py:189).  `blob_host`: conv1d_1 weight [F,d_in,k], bias, layer_norm_1 gamma,
+ *   beta, conv1d_2 weight [F,F,k], bias, layer_norm_2 gamma, beta, linear_layer weight [F], bias [1].
+ * vo2w_variance_embed: replaces get_energy_embedding / get_kurtosis_embedding (modules.py:53-78) after the predictor:
+ *   denorm != 0 (no target given): v = ((value * std + mean) * control - mean) / std, each step rounded to fp32 as
+ *   the reference's tensor-scalar ops are; denorm == 0 (a target is given): v = value.  Then
+ *   out[r,:] = x[r,:] + table[bucketize(v, bins)]  with torch.bucketize's right=False rule (first edge >= v);
+ *   value_out (optional) receives v.  bins [n_edges] ascending, table [n_edges+1, D].
+ * vo2w_duration_round: out = clamp(round(exp(log_duration) - 1) * d_control, min=0), round half to even
+ *   (modules.py:110-113); the float durations feed vo2w_length_regulate (VO2W_DUR_F32) unchanged. */
+typedef struct vo2w_varpred vo2w_varpred;
+int vo2w_varpred_create(int d_in, int d_filter, int k, const float* blob_host, size_t n_floats, vo2w_varpred** out);
+int vo2w_varpred_destroy(vo2w_varpred* p);
+size_t vo2w_varpred_workspace_bytes(const vo2w_varpred* p, int B, int T);
+int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8_t* mask, int B, int T, float* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int vo2w_variance_embed(const float* x, const float* value, const float* bins, int n_edges, const float* table,
+                        float mean, float stdv, float control, int denorm, float* value_out, float* out,
+                        long long rows, int D, void* stream);
+int vo2w_duration_round(const float* log_duration, float d_control, float* out, long long n, void* stream);
+
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad
  * (scripts/utils/tools.py:669-687).

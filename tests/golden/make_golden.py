@@ -195,7 +195,64 @@ def decoder_golden():
     print("decoder.npz written")
 
 
+def variance_golden():
+    """VarianceAdaptor in front of LengthRegulator, outputs of the reference's own classes.
+    Seeds are walked until every predicted value sits clear of a rounding / bin edge, so that a 1e-6 difference in a
+    predictor output cannot flip an integer on the other side."""
+    import tempfile
+    from visual_onoma_to_wave_b200.synthetic import (seeded_variance_adaptor_state_dict, variance_model_config,
+                                                     VARIANCE_STATS)
+    import model.modules as mm               # reference
+    mm.device = torch.device("cpu")          # module-global device (modules.py:13)
+    import utils.tools as ut
+    ut.device = torch.device("cpu")
+    tmp = tempfile.mkdtemp()
+    with open(os.path.join(tmp, "stats.json"), "w") as f:
+        json.dump(VARIANCE_STATS, f)
+    pre_cfg = {"path": {"preprocessed": tmp}}
+    out = {}
+    cases = {"energy": dict(is_energy=True, is_kurtosis=False), "both": dict(is_energy=True, is_kurtosis=True)}
+    for name, kw in cases.items():
+        lens = [29, 17, 5]
+        B, T = len(lens), max(lens)
+        src_mask = torch.arange(T)[None, :] >= torch.tensor(lens)[:, None]
+        for seed in range(1357, 1457):
+            sd = seeded_variance_adaptor_state_dict(seed, **kw)
+            va = mm.VarianceAdaptor(pre_cfg, variance_model_config(**kw))
+            va.load_state_dict(sd)           # strict: the key set is the reference's
+            va.eval()
+            x = torch.randn(B, T, 256, generator=torch.Generator().manual_seed(seed + 1))
+            with torch.no_grad():
+                r = va(x, src_mask, e_control=1.2, d_control=1.5)
+                frac = torch.exp(r[3]) - 1
+                ok = float(((frac - torch.floor(frac)) - 0.5).abs().min()) > 2e-3
+                ok = ok and float((r[1][..., None] - sd["energy_bins"]).abs().min()) > 2e-4
+                if kw["is_kurtosis"]:
+                    ok = ok and float((r[2][..., None] - sd["kurt_bins"]).abs().min()) > 2e-4
+            if ok:
+                break
+        assert ok, "no seed with safe margins"
+        with torch.no_grad():
+            et = torch.rand(B, T, generator=torch.Generator().manual_seed(3)) * 8 - 1
+            dt = torch.randint(0, 7, (B, T), generator=torch.Generator().manual_seed(4))
+            rt = va(x, src_mask, mel_mask=None, max_len=100, energy_target=et, duration_target=dt)
+        out[f"seed_{name}"] = np.array(seed)
+        out[f"sha_{name}"] = np.frombuffer(sd_sha256(sd).encode(), dtype=np.uint8)
+        out[f"x_{name}"], out[f"mask_{name}"] = x.numpy(), src_mask.numpy()
+        keys = ["out", "e_pred", "k_pred", "log_d", "d_round", "mel_len", "mel_mask"]
+        for k, val in zip(keys, r):
+            if val is not None:
+                out[f"{k}_{name}"] = val.numpy()
+        out[f"et_{name}"], out[f"dt_{name}"] = et.numpy(), dt.numpy()
+        for k, val in zip(keys, rt):
+            if val is not None:
+                out[f"t_{k}_{name}"] = val.numpy()
+    np.savez_compressed(os.path.join(HERE, "variance.npz"), **out)
+    print("variance.npz written", {k: int(out[k]) for k in out if k.startswith("seed_")})
+
+
 if __name__ == "__main__":
     main()
     postnet_golden()
     decoder_golden()
+    variance_golden()

@@ -409,6 +409,90 @@ def test_decoder_against_oracle_ragged_batch(dev):
     assert float((got.cpu() - ref).abs().max()) <= DECODER_TOL
 
 
+VARIANCE_CASES = {"energy": dict(is_energy=True, is_kurtosis=False), "both": dict(is_energy=True, is_kurtosis=True)}
+VARIANCE_KEYS = ["out", "e_pred", "k_pred", "log_d", "d_round", "mel_len", "mel_mask"]
+VARIANCE_TOL = 1e-4
+
+
+def _check_variance_tuple(got, g, name, prefix):
+    for k, val in zip(VARIANCE_KEYS, got):
+        key = f"{prefix}{k}_{name}"
+        if key not in g.files:
+            assert val is None or k == "mel_mask", key
+            continue
+        ref = torch.from_numpy(g[key])
+        val = val.cpu()
+        assert val.shape == ref.shape, key
+        if ref.dtype in (torch.int64, torch.bool) or k == "d_round":       # integers: bit-exact
+            assert torch.equal(val.to(ref.dtype), ref), key
+        else:
+            assert float((val - ref).abs().max()) <= VARIANCE_TOL, key
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(VARIANCE_CASES))
+def test_variance_adaptor_against_reference_golden(dev, golden_dir, tmp_path, name):
+    import json
+    from visual_onoma_to_wave_b200.synthetic import (seeded_variance_adaptor_state_dict, variance_model_config,
+                                                     VARIANCE_STATS)
+    g = np.load(os.path.join(golden_dir, "variance.npz"))
+    kw = VARIANCE_CASES[name]
+    (tmp_path / "stats.json").write_text(json.dumps(VARIANCE_STATS))
+    va = v.VarianceAdaptor({"path": {"preprocessed": str(tmp_path)}}, variance_model_config(**kw))
+    va.load_state_dict(seeded_variance_adaptor_state_dict(int(g[f"seed_{name}"]), **kw))
+    va.eval().to(dev)
+    x, mask = torch.from_numpy(g[f"x_{name}"]).to(dev), torch.from_numpy(g[f"mask_{name}"]).to(dev)
+    _check_variance_tuple(va(x, mask, e_control=1.2, d_control=1.5), g, name, "")
+    got = va(x, mask, mel_mask=None, max_len=100, energy_target=torch.from_numpy(g[f"et_{name}"]).to(dev),
+             duration_target=torch.from_numpy(g[f"dt_{name}"]).to(dev))
+    _check_variance_tuple(got, g, name, "t_")
+
+
+@pytest.mark.gpu
+def test_variance_pieces_against_oracle(dev):
+    """Batch-64 predictor, bucketize on exact edges, duration rounding on exact halves."""
+    from oracle import variance_oracle as vo
+    from oracle import length_regulator_oracle as lro
+    from visual_onoma_to_wave_b200.synthetic import seeded_variance_adaptor_state_dict, variance_model_config
+    from visual_onoma_to_wave_b200.variance_adaptor import variance_embed, duration_round
+    sd = seeded_variance_adaptor_state_dict(77)
+    vp = v.VariancePredictor(variance_model_config())
+    vp.load_state_dict({k[len("energy_predictor."):]: t for k, t in sd.items() if k.startswith("energy_predictor.")})
+    vp.eval().to(dev)
+    lens = torch.randint(1, 33, (64,), generator=torch.Generator().manual_seed(1))
+    lens[0] = 32
+    x = torch.randn(64, 32, 256, generator=torch.Generator().manual_seed(2))
+    mask = torch.arange(32)[None, :] >= lens[:, None]
+    ref = vo.variance_predictor(sd, "energy_predictor.", x, mask)
+    assert float((vp(x.to(dev), mask.to(dev)).cpu() - ref).abs().max()) <= VARIANCE_TOL
+    assert float((vp(x.to(dev), None).cpu() - vo.variance_predictor(sd, "energy_predictor.", x, None)).abs().max()) <= VARIANCE_TOL
+    # bucketize: values exactly on edges, below the first and above the last edge
+    bins, table = sd["energy_bins"], sd["energy_embedding.weight"]
+    val = torch.cat([bins[:60], bins[:60] + 1e-3, torch.tensor([-1e9, 1e9, 0.0, -0.0])]).reshape(4, 31)
+    xs = torch.randn(4, 31, 256, generator=torch.Generator().manual_seed(3))
+    v_out, y = variance_embed(xs.to(dev), val.to(dev), bins, table, denorm=False)
+    assert torch.equal(v_out.cpu(), val)
+    assert torch.equal(y.cpu(), xs + table[torch.bucketize(val, bins)])
+    # the de-normalise / control / re-normalise chain, bit for bit (no FMA contraction)
+    pred = torch.randn(4, 31, generator=torch.Generator().manual_seed(4)) * 2
+    v_out, y = variance_embed(xs.to(dev), pred.to(dev), bins, table, 37.32, 26.08, 1.3, denorm=True)
+    want = (((pred * 26.08 + 37.32) * 1.3) - 37.32) / 26.08          # modules.py:59-61, fp32 tensor-scalar ops
+    assert torch.equal(v_out.cpu(), want)
+    assert torch.equal(y.cpu(), xs + table[torch.bucketize(want, bins)])
+    with pytest.raises(RuntimeError):           # the reference's fixed padding=1 only fits kernel_size 3
+        v.VariancePredictor(variance_model_config(kernel=5)).eval().to(dev)(x.to(dev), None)
+    # duration rounding: exact halves round to even, negatives clamp to zero
+    k = torch.arange(0, 40, dtype=torch.float32)
+    ld = torch.cat([torch.log(k + 1.5), torch.tensor([-3.0, -0.5, 0.0, 3.3])])
+    got = duration_round(ld.to(dev), 1.0).cpu()
+    want = torch.from_numpy(lro.round_durations(ld.numpy(), 1.0))
+    near_half = ((torch.exp(ld) - 1) % 1 - 0.5).abs() < 1e-4        # log/exp round trip is not exact: skip ties it moved
+    assert torch.equal(got[~near_half], want[~near_half])
+    assert float((got - want).abs().max()) <= 1.0
+    assert torch.equal(duration_round(torch.tensor([1.0, 2.0, -5.0]).to(dev), 0.5).cpu(),
+                       torch.clamp(torch.round(torch.exp(torch.tensor([1.0, 2.0, -5.0])) - 1) * 0.5, min=0))
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

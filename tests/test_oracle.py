@@ -197,3 +197,58 @@ def test_decoder_dropin_has_the_reference_state_dict_keys():
         dec(torch.zeros(1, 4, 256), mask)
     D, H = 256, 256
     assert dec.weight_blob().numel() == 2 * (4 * D * D + 4 * D + 4 * D + H * D * 3 + H + D * H + D)
+
+
+# ------------------------------------------------------------------------------------------
+# VarianceAdaptor: the oracle against outputs of the reference classes
+# ------------------------------------------------------------------------------------------
+VARIANCE_CASES = {"energy": dict(is_energy=True, is_kurtosis=False), "both": dict(is_energy=True, is_kurtosis=True)}
+VARIANCE_KEYS = ["out", "e_pred", "k_pred", "log_d", "d_round", "mel_len", "mel_mask"]
+
+
+def _check_variance_tuple(got, g, name, prefix, tol):
+    for k, val in zip(VARIANCE_KEYS, got):
+        key = f"{prefix}{k}_{name}"
+        if key not in g.files:
+            assert val is None or k == "mel_mask", key      # mel_mask=None passes through on the target path
+            continue
+        ref = torch.from_numpy(g[key])
+        val = val.cpu()
+        assert val.shape == ref.shape, key
+        if ref.dtype in (torch.int64, torch.bool) or k == "d_round":
+            assert torch.equal(val.to(ref.dtype), ref), key
+        else:
+            assert float((val - ref).abs().max()) <= tol, key
+
+
+@pytest.mark.parametrize("name", list(VARIANCE_CASES))
+def test_variance_oracle_matches_reference_golden(golden_dir, name):
+    from oracle import variance_oracle as vo
+    from visual_onoma_to_wave_b200.synthetic import seeded_variance_adaptor_state_dict, VARIANCE_STATS
+    g = np.load(os.path.join(golden_dir, "variance.npz"))
+    kw = VARIANCE_CASES[name]
+    sd = seeded_variance_adaptor_state_dict(int(g[f"seed_{name}"]), **kw)
+    assert _sha(sd) == bytes(g[f"sha_{name}"]), "seeded VarianceAdaptor weights drifted from the fixture"
+    x, mask = torch.from_numpy(g[f"x_{name}"]), torch.from_numpy(g[f"mask_{name}"])
+    got = vo.variance_adaptor_forward(sd, VARIANCE_STATS, x, mask, e_control=1.2, d_control=1.5, **kw)
+    _check_variance_tuple(got, g, name, "", 2e-5)
+    got = vo.variance_adaptor_forward(sd, VARIANCE_STATS, x, mask, max_len=100, energy_target=torch.from_numpy(g[f"et_{name}"]),
+                                      duration_target=torch.from_numpy(g[f"dt_{name}"]), **kw)
+    _check_variance_tuple(got, g, name, "t_", 2e-5)
+
+
+def test_variance_adaptor_dropin_has_the_reference_state_dict_keys(tmp_path):
+    import json
+    import visual_onoma_to_wave_b200 as v
+    from visual_onoma_to_wave_b200.synthetic import (seeded_variance_adaptor_state_dict, variance_model_config,
+                                                     VARIANCE_STATS)
+    (tmp_path / "stats.json").write_text(json.dumps(VARIANCE_STATS))
+    kw = dict(is_energy=True, is_kurtosis=True)
+    va = v.VarianceAdaptor({"path": {"preprocessed": str(tmp_path)}}, variance_model_config(**kw))
+    sd = seeded_variance_adaptor_state_dict(1, **kw)
+    assert set(va.state_dict().keys()) == set(sd.keys())
+    va.load_state_dict(sd)                      # strict
+    assert torch.equal(va.energy_bins, sd["energy_bins"])      # the constructor's own edges are the reference's
+    va.eval()
+    with pytest.raises(RuntimeError):           # no CPU fallback
+        va(torch.zeros(1, 4, 256), torch.zeros(1, 4, dtype=torch.bool))

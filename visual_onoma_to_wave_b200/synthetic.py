@@ -137,3 +137,42 @@ def decoder_config(d_model: int = 256, n_head: int = 2, d_inner: int = 1024, ker
     return {"max_seq_len": max_seq_len,
             "transformer": {"decoder_hidden": d_model, "decoder_layer": n_layers, "decoder_head": n_head,
                             "conv_filter_size": d_inner, "conv_kernel_size": list(kernels), "decoder_dropout": 0.2}}
+
+
+VARIANCE_STATS = {"energy": [-1.431, 8.012, 37.32, 26.08], "kurtosis": [-1.207, 9.034, 3.127, 2.215]}   # a stats.json
+
+
+def variance_model_config(d_hidden: int = 256, filter_size: int = 256, kernel: int = 3, n_bins: int = 256,
+                          is_energy: bool = True, is_kurtosis: bool = False):
+    """The slice of config/*/model.yaml VarianceAdaptor / VariancePredictor read (modules.py:17-50, 164-170)."""
+    return {"transformer": {"encoder_hidden": d_hidden},
+            "variance_predictor": {"filter_size": filter_size, "kernel_size": kernel, "dropout": 0.5},
+            "variance_embedding": {"is_kurtosis_condition": is_kurtosis, "is_energy_condition": is_energy,
+                                   "kurtosis_quantization": "linear", "energy_quantization": "linear", "n_bins": n_bins}}
+
+
+def seeded_variance_adaptor_state_dict(seed: int = 1357, d_hidden: int = 256, filter_size: int = 256, kernel: int = 3,
+                                       n_bins: int = 256, is_energy: bool = True, is_kurtosis: bool = False,
+                                       stats=VARIANCE_STATS):
+    """State dict with the reference VarianceAdaptor's keys (scripts/model/modules.py:17-50): seeded predictors whose
+    outputs spread over the bins / over durations 0..~30, linear bin edges from `stats`, seeded embedding tables."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    preds = ["duration_predictor"] + (["kurtosis_predictor"] if is_kurtosis else []) + (["energy_predictor"] if is_energy else [])
+    for name in preds:
+        p = name + "."
+        sd[p + "conv_layer.conv1d_1.conv.weight"] = torch.randn(filter_size, d_hidden, kernel, generator=g) * (1.4 / (d_hidden * kernel) ** 0.5)
+        sd[p + "conv_layer.conv1d_1.conv.bias"] = torch.randn(filter_size, generator=g) * 0.1
+        sd[p + "conv_layer.layer_norm_1.weight"] = torch.rand(filter_size, generator=g) + 0.5
+        sd[p + "conv_layer.layer_norm_1.bias"] = torch.randn(filter_size, generator=g) * 0.1
+        sd[p + "conv_layer.conv1d_2.conv.weight"] = torch.randn(filter_size, filter_size, kernel, generator=g) * (1.4 / (filter_size * kernel) ** 0.5)
+        sd[p + "conv_layer.conv1d_2.conv.bias"] = torch.randn(filter_size, generator=g) * 0.1
+        sd[p + "conv_layer.layer_norm_2.weight"] = torch.rand(filter_size, generator=g) + 0.5
+        sd[p + "conv_layer.layer_norm_2.bias"] = torch.randn(filter_size, generator=g) * 0.1
+        sd[p + "linear_layer.weight"] = torch.randn(1, filter_size, generator=g) * 0.06
+        sd[p + "linear_layer.bias"] = torch.tensor([1.2 if name == "duration_predictor" else 0.3])
+    sd["kurt_bins"] = torch.linspace(stats["kurtosis"][0], stats["kurtosis"][1], n_bins - 1)
+    sd["kurt_embedding.weight"] = torch.randn(n_bins, d_hidden, generator=g)
+    sd["energy_bins"] = torch.linspace(stats["energy"][0], stats["energy"][1], n_bins - 1)
+    sd["energy_embedding.weight"] = torch.randn(n_bins, d_hidden, generator=g)
+    return sd
