@@ -156,7 +156,8 @@ int vo2w_generator_get_timing(vo2w_generator* g, float* ms, int32_t* kind, int c
  * 4 x tanh(BatchNorm1d(Conv1d k)) -> BatchNorm1d(Conv1d k) -> [B,L,n_mel].  `folded_host` holds, per convolution,
  * weight [Cout,Cin,k] then bias [Cout] with the eval-mode BatchNorm already folded in by the caller
  * (w' = w * g / sqrt(var + eps), b' = (b - mean) * g / sqrt(var + eps) + beta).  add_input != 0 returns
- * postnet(x) + x, the `postnet_output` of vTTS.forward (scripts/model/vtts.py:107).  fp32 CUDA-core path. */
+ * postnet(x) + x, the `postnet_output` of vTTS.forward (scripts/model/vtts.py:107).  Tensor pipe with fp32-level
+ * accuracy (conv_tf32.cu) when n_mel % 16 == 0 and dim % 64 == 0, else fp32 CUDA cores. */
 typedef struct vo2w_postnet vo2w_postnet;
 int vo2w_postnet_create(int n_mel, int dim, int k, int n_conv, const float* folded_host, size_t n_floats,
                         vo2w_postnet** out);
@@ -166,9 +167,11 @@ int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int L, float* o
                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* nn.Linear on the last axis (mel_linear, scripts/model/vtts.py:106): y[r,:] = W x[r,:] + b for `rows` rows;
- * x [rows,K], w [N,K], bias [N] or NULL, y [rows,N], all fp32 on the device. */
+ * x [rows,K], w [N,K], bias [N] or NULL, y [rows,N], all fp32 on the device.  `scratch` (2*N*K floats on the device,
+ * or NULL) lets shapes the tensor-pipe kernel tiles (K % 8 == 0; N % 64 == 0 or N <= 128 and N % 16 == 0) run
+ * there; without it, or for other shapes, an fp32 CUDA-core kernel does the work. */
 int vo2w_linear_forward(const float* x, const float* w, const float* bias, long long rows, int K, int N,
-                        float* y, void* stream);
+                        float* y, float* scratch, void* stream);
 
 /* ---- mel Decoder: the FFT-block stack ----------------------------
  * Replaces Decoder.forward (scripts/transformer/Models.py:168-197) in eval mode:
@@ -180,7 +183,8 @@ int vo2w_linear_forward(const float* x, const float* w, const float* bias, long 
  * table built the same way when L > max_seq_len, Models.py:175-181); mask [B,L] bytes, 1 = padding frame, or NULL.
  * Head size d_model / n_head must be 128 (the reference's 256 / 2).  `blob_host`, per layer: [w_qs|w_ks|w_vs]
  * [3D,D], their biases [3D], fc [D,D], bias, attention LayerNorm gamma, beta, w_1 [d_inner,D,k1], bias,
- * w_2 [D,d_inner,k2], bias, feed-forward LayerNorm gamma, beta.  fp32 CUDA-core path. */
+ * w_2 [D,d_inner,k2], bias, feed-forward LayerNorm gamma, beta.  d_inner % 64 == 0.  Linear / Conv1d layers on the
+ * tensor pipe with fp32-level accuracy (conv_tf32.cu), attention and LayerNorm on fp32 CUDA cores. */
 typedef struct vo2w_decoder vo2w_decoder;
 int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1, int k2, int n_layers, const float* blob_host,
                         size_t n_floats, vo2w_decoder** out);
@@ -212,6 +216,14 @@ int vo2w_variance_embed(const float* x, const float* value, const float* bins, i
                         float mean, float stdv, float control, int denorm, float* value_out, float* out,
                         long long rows, int D, void* stream);
 int vo2w_duration_round(const float* log_duration, float d_control, float* out, long long n, void* stream);
+
+/* Test / profiling entry for the fp32-accurate tensor-pipe convolution of the acoustic tail (conv_tf32.cu):
+ * out[b,l,:] = act(bias + res[b,l,:] + sum_j W[:,:,j] x[b,l+j-(k-1)/2,:]), time-major x [B,L,Cin], out/res [B,L,Cout],
+ * w [Cout,Cin,k] (Conv1d layout; k=1 is nn.Linear), act 0 none / 1 relu / 2 tanh; bias, res may be NULL.
+ * `scratch` (2*Cout*Cin*k floats) receives the packed weights.  Cin % 8 == 0; Cout % 64 == 0, or Cout <= 128 and
+ * Cout % 16 == 0. */
+int vo2w_debug_tf32_conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int L,
+                         int Cin, int Cout, int k, int act, float* scratch, void* stream);
 
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad

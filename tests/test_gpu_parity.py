@@ -493,6 +493,104 @@ def test_variance_pieces_against_oracle(dev):
                        torch.clamp(torch.round(torch.exp(torch.tensor([1.0, 2.0, -5.0])) - 1) * 0.5, min=0))
 
 
+@pytest.mark.gpu
+def test_acoustic_tail_chain_against_oracles(dev, tmp_path, gens):
+    """vtts.py:84-107 behind the encoder, then the vocoder: adaptor -> decoder -> mel_linear -> postnet -> wav."""
+    import json
+    from oracle import variance_oracle as vo, decoder_oracle as do, postnet_oracle as po, hifigan_oracle as ho
+    from visual_onoma_to_wave_b200.synthetic import (seeded_variance_adaptor_state_dict, variance_model_config,
+                                                     seeded_decoder_state_dict, decoder_config, seeded_postnet_state_dict,
+                                                     VARIANCE_STATS)
+    (tmp_path / "stats.json").write_text(json.dumps(VARIANCE_STATS))
+    dkw = dict(n_layers=2)
+    model_config = {**variance_model_config(), **decoder_config(**dkw)}
+    model_config["transformer"]["encoder_hidden"] = 256
+    pre_cfg = {"path": {"preprocessed": str(tmp_path)}, "preprocessing": {"mel": {"n_mel_channels": 80}}}
+    lens = torch.tensor([20, 13, 20, 7])
+    src_mask = torch.arange(20)[None, :] >= lens[:, None]
+    g = torch.Generator().manual_seed(21)
+    lin_w, lin_b = torch.randn(80, 256, generator=g) / 16, torch.randn(80, generator=g) * 0.1 - 4.0
+    for seed in range(500, 540):        # walk to a seed whose predictions sit clear of rounding / bin edges
+        sd_va = seeded_variance_adaptor_state_dict(seed)
+        x = torch.randn(4, 20, 256, generator=torch.Generator().manual_seed(seed))
+        ref = vo.variance_adaptor_forward(sd_va, VARIANCE_STATS, x, src_mask, d_control=0.8)
+        frac = torch.exp(ref[3]) - 1
+        if float(((frac - torch.floor(frac)) - 0.5).abs().min()) > 2e-3 and \
+                float((ref[1][..., None] - sd_va["energy_bins"]).abs().min()) > 2e-4:
+            break
+    sd_dec, sd_pn = seeded_decoder_state_dict(seed, **dkw), seeded_postnet_state_dict(seed)
+    dec_ref, _ = do.decoder_forward(sd_dec, ref[0], ref[6])
+    mel_ref, post_ref = po.vtts_tail(sd_pn, lin_w, lin_b, dec_ref)
+
+    tail = v.AcousticTail(pre_cfg, model_config)
+    sd = {**{"variance_adaptor." + k: t for k, t in sd_va.items()}, **{"decoder." + k: t for k, t in sd_dec.items()},
+          **{"postnet." + k: t for k, t in sd_pn.items()}, "mel_linear.weight": lin_w, "mel_linear.bias": lin_b}
+    assert set(tail.state_dict().keys()) == set(sd.keys())
+    tail.load_state_dict(sd)
+    tail.eval().to(dev)
+    out, post, e_pred, k_pred, log_d, d_round, mel_mask, mel_len = tail(x.to(dev), src_mask.to(dev), d_control=0.8)
+    assert k_pred is None
+    assert torch.equal(d_round.cpu(), ref[4]) and torch.equal(mel_len.cpu(), ref[5]) and torch.equal(mel_mask.cpu(), ref[6])
+    assert float((log_d.cpu() - ref[3]).abs().max()) <= VARIANCE_TOL
+    assert float((e_pred.cpu() - ref[1]).abs().max()) <= VARIANCE_TOL
+    assert float((out.cpu() - mel_ref).abs().max()) <= 2e-4
+    assert float((post.cpu() - post_ref).abs().max()) <= 2e-4
+    # a second load through the parent replaces the device copies of every sub-module
+    sd2 = dict(sd)
+    sd2["mel_linear.bias"] = lin_b + 1.0
+    sd2["decoder.layer_stack.0.slf_attn.fc.bias"] = sd["decoder.layer_stack.0.slf_attn.fc.bias"] + 0.5
+    tail.load_state_dict(sd2)
+    out2 = tail(x.to(dev), src_mask.to(dev), d_control=0.8)[0]
+    assert float((out2 - out).abs().max()) > 0.5
+    # mel -> waveform, the order of synth_samples (scripts/utils/tools.py:360-375): fp32 mode against the oracle
+    gen_map, sd_gen = gens
+    mel = post.transpose(1, 2).contiguous()
+    wav = gen_map["fp32"](mel).cpu()
+    wav_ref = ho.generator_forward(sd_gen, post_ref.transpose(1, 2).contiguous())
+    assert float((wav - wav_ref).abs().max()) <= 1e-3      # 2e-4 of mel error through the vocoder's gain
+
+
+TF32_SHAPES = [  # B, L, Cin, Cout, k, act, res      (the acoustic tail's layers + ragged / tiny edge cases)
+    (3, 479, 256, 1024, 9, 1, False),    # FFN w_1 + relu
+    (3, 479, 1024, 256, 1, 0, True),     # FFN w_2 + residual
+    (2, 300, 256, 768, 1, 0, False),     # q|k|v projection
+    (2, 131, 80, 512, 5, 2, False),      # PostNet first convolution + tanh
+    (2, 257, 512, 80, 5, 0, False),      # PostNet last convolution (80-wide tile)
+    (5, 7, 256, 80, 1, 0, False),        # mel_linear on very short utterances
+    (1, 128, 8, 64, 3, 0, True),
+    (2, 129, 16, 192, 11, 1, True),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", TF32_SHAPES)
+def test_tf32_split_convolution_is_fp32_accurate(dev, shape):
+    """tcgen05 kind::tf32 with the hi/lo operand split against an fp64 convolution.  A single-pass TF32 product is
+    ~1e-3 off here; the split leaves the tensor pipe's truncating fp32 accumulation, ~1e-7 per accumulation of the
+    hi.hi chain (K/8 of them): 3e-5 max-abs at K = 2304 on O(1) outputs, 5e-6 at K = 256."""
+    import torch.nn.functional as F
+    B, L, Cin, Cout, k, act, use_res = shape
+    g = torch.Generator().manual_seed(Cin * 7 + Cout + k)
+    x = torch.randn(B, L, Cin, generator=g)
+    w = torch.randn(Cout, Cin, k, generator=g) / (Cin * k) ** 0.5
+    bias = torch.randn(Cout, generator=g)
+    res = torch.randn(B, L, Cout, generator=g) if use_res else None
+    ref = F.conv1d(x.double().transpose(1, 2), w.double(), bias.double(), padding=(k - 1) // 2).transpose(1, 2)
+    if use_res:
+        ref = ref + res.double()
+    ref = torch.relu(ref) if act == 1 else (torch.tanh(ref) if act == 2 else ref)
+    xd, wd, bd = x.to(dev), w.to(dev), bias.to(dev)
+    rd = res.to(dev) if use_res else None
+    out = torch.full((B, L, Cout), float("nan"), device=dev)
+    scratch = torch.empty(2 * w.numel(), device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().vo2w_debug_tf32_conv(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), rd.data_ptr() if use_res else None,
+                                                   out.data_ptr(), B, L, Cin, Cout, k, act, scratch.data_ptr(),
+                                                   torch.cuda.current_stream(dev).cuda_stream), "vo2w_debug_tf32_conv")
+    err = float((out.cpu().double() - ref).abs().max())
+    assert err <= 4e-6 + 2e-8 * Cin * k, err
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

@@ -18,9 +18,10 @@ from .length_regulator import LengthRegulator, get_mask_from_lengths, round_dura
 from .vocoder import get_vocoder, vocoder_infer  # noqa: F401
 from .postnet import PostNet, ConvNorm, mel_linear  # noqa: F401
 from .variance_adaptor import VarianceAdaptor, VariancePredictor, Conv  # noqa: F401
+from .acoustic_tail import AcousticTail  # noqa: F401
 from .decoder import Decoder, FFTBlock, MultiHeadAttention, PositionwiseFeedForward  # noqa: F401
 from .sharding import shard_bounds  # noqa: F401
 
 __all__ = ["hifigan", "AttrDict", "Generator", "LengthRegulator", "get_mask_from_lengths", "round_durations",
            "get_vocoder", "vocoder_infer", "shard_bounds", "PostNet", "ConvNorm", "mel_linear",
-           "VarianceAdaptor", "VariancePredictor", "Conv", "Decoder", "FFTBlock", "MultiHeadAttention", "PositionwiseFeedForward"]
+           "AcousticTail", "VarianceAdaptor", "VariancePredictor", "Conv", "Decoder", "FFTBlock", "MultiHeadAttention", "PositionwiseFeedForward"]

@@ -58,7 +58,7 @@ SYMBOLS = {
     "vo2w_postnet_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                        C.c_size_t, C.c_void_p]),
     "vo2w_linear_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p,
-                                      C.c_void_p]),
+                                      C.c_void_p, C.c_void_p]),
     "vo2w_decoder_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
                                       C.POINTER(C.c_void_p)]),
     "vo2w_decoder_destroy": (C.c_int, [C.c_void_p]),
@@ -73,6 +73,8 @@ SYMBOLS = {
     "vo2w_variance_embed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float,
                                       C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
     "vo2w_duration_round": (C.c_int, [C.c_void_p, C.c_float, C.c_void_p, C.c_longlong, C.c_void_p]),
+    "vo2w_debug_tf32_conv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "vo2w_lr_lengths": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vo2w_length_regulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
                                        C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]),

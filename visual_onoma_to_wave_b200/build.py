@@ -8,8 +8,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvo2w.so")
-SOURCES = ["errors.cu", "lr.cu", "conv_simt.cu", "conv_umma.cu", "pack.cu", "pair_umma.cu", "generator.cu", "rows.cu", "postnet.cu", "decoder.cu", "variance.cu"]
-HEADERS = ["common.cuh", "conv_simt.cuh", "conv_umma.cuh", "pack.cuh", "pair_umma.cuh", "rows.cuh", "../../include/vo2w.h"]
+SOURCES = ["errors.cu", "lr.cu", "conv_simt.cu", "conv_tf32.cu", "conv_umma.cu", "pack.cu", "pair_umma.cu", "generator.cu", "rows.cu", "postnet.cu", "decoder.cu", "variance.cu"]
+HEADERS = ["common.cuh", "conv_simt.cuh", "conv_tf32.cuh", "conv_umma.cuh", "pack.cuh", "pair_umma.cuh", "rows.cuh", "../../include/vo2w.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

@@ -7,13 +7,13 @@
 //       PositionwiseFeedForward (SubLayers.py:95-104): LayerNorm(w_2(relu(w_1(x^T)))^T + x);  masked_fill(mask, 0)
 //   (dropout is the identity in eval mode).
 //
-// fp32 CUDA-core path.  The stack runs channel-major ([B,D,L], one tiled transpose in and one out): every Linear is
-// a k=1 convolution on the exact-mode convolution kernel (conv_simt.cu, q|k|v fused into one [3D,D] layer, the fc
-// and w_2 layers fuse their residual add), attention is a tiled online-softmax kernel (64 queries x 64 keys per
-// step, d_k = 128), LayerNorm + padding mask one kernel over the channel axis.
+// Time-major [B,L,D] rows throughout (the reference's own layout: no transposes).  Every Linear / Conv1d runs on the
+// tensor pipe with fp32-level accuracy (conv_tf32.cu: kind::tf32 with a hi/lo operand split; q|k|v fused into one
+// [3D,D] layer, relu and the residual adds fused into the epilogues), attention is a tiled online-softmax kernel
+// (64 queries x 64 keys per step, d_k = 128, fp32 CUDA cores), LayerNorm + padding mask one warp-per-row kernel.
 #include <vector>
 
-#include "conv_simt.cuh"
+#include "conv_tf32.cuh"
 #include "rows.cuh"
 
 namespace {
@@ -23,7 +23,7 @@ constexpr int AQS = AD + 1, APS = AK + 1;           // padded shared-memory stri
 constexpr size_t ATTN_SMEM = ((size_t)AQ * AQS + (size_t)AK * AQS + (size_t)AQ * APS + 3 * AQ) * 4;
 
 // out[b, q, h*128 + :] = softmax_k(q_h . k_h / sqrt(128) masked) v_h   for one (query tile, head, utterance)
-// qkv [B][3*D][L] (q | k | v channels, head h at channels h*128), mask [B][L] (1 = padding key) or null, out [B][D][L]
+// qkv [B*L][3*D] rows (q | k | v, head h at columns h*128), mask [B][L] (1 = padding key) or null, out [B*L][D]
 __global__ void __launch_bounds__(256) attention_kernel(const float* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                         float* __restrict__ out, int L, int D, float scale) {
     extern __shared__ float sm[];
@@ -35,12 +35,13 @@ __global__ void __launch_bounds__(256) attention_kernel(const float* __restrict_
     float* rowA = rowL + AQ;
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * AQ;
     const int tid = threadIdx.x, tq = tid >> 4, tk = tid & 15, warp = tid >> 5, lane = tid & 31;
-    const float* base = qkv + ((size_t)b * 3 * D + (size_t)h * AD) * L;      // element (channel d, time t) at base[d * L + t]
+    const size_t row_stride = (size_t)3 * D;
+    const float* base = qkv + (size_t)b * L * row_stride + (size_t)h * AD;
     const uint8_t* mb = mask ? mask + (size_t)b * L : nullptr;
 
     for (int e = tid; e < AQ * AD; e += 256) {
-        const int d = e >> 6, r = e & 63;                       // time fastest: coalesced
-        Qs[r * AQS + d] = (q0 + r < L) ? base[(size_t)d * L + q0 + r] * scale : 0.f;
+        const int r = e >> 7, d = e & 127;
+        Qs[r * AQS + d] = (q0 + r < L) ? base[(size_t)(q0 + r) * row_stride + d] * scale : 0.f;
     }
     if (tid < AQ) { rowM[tid] = -1e30f; rowL[tid] = 0.f; rowA[tid] = 0.f; }
     float O[4][8];
@@ -52,8 +53,8 @@ __global__ void __launch_bounds__(256) attention_kernel(const float* __restrict_
 
     for (int k0 = 0; k0 < L; k0 += AK) {
         for (int e = tid; e < AK * AD; e += 256) {
-            const int d = e >> 6, r = e & 63;
-            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(D + d) * L + k0 + r] : 0.f;
+            const int r = e >> 7, d = e & 127;
+            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(k0 + r) * row_stride + D + d] : 0.f;
         }
         __syncthreads();
         float S[4][4];
@@ -102,8 +103,8 @@ __global__ void __launch_bounds__(256) attention_kernel(const float* __restrict_
         }
         __syncthreads();
         for (int e = tid; e < AK * AD; e += 256) {                  // values over the keys
-            const int d = e >> 6, r = e & 63;
-            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(2 * D + d) * L + k0 + r] : 0.f;
+            const int r = e >> 7, d = e & 127;
+            KVs[r * AQS + d] = (k0 + r < L) ? base[(size_t)(k0 + r) * row_stride + 2 * D + d] : 0.f;
         }
         __syncthreads();
 #pragma unroll
@@ -125,66 +126,67 @@ __global__ void __launch_bounds__(256) attention_kernel(const float* __restrict_
         }
         __syncthreads();
     }
-    // through shared memory (the query tile is dead) so that the channel-major store is coalesced along time
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
+        const int q = q0 + tq * 4 + i;
+        if (q >= L) continue;
         const float inv = 1.f / rowL[tq * 4 + i];
+        float* o = out + ((size_t)b * L + q) * D + (size_t)h * AD;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) Qs[(tq * 4 + i) * AQS + tk + 16 * e] = O[i][e] * inv;
-    }
-    __syncthreads();
-    float* ob = out + ((size_t)b * D + (size_t)h * AD) * L;
-    for (int e = tid; e < AQ * AD; e += 256) {
-        const int d = e >> 6, r = e & 63;
-        if (q0 + r < L) ob[(size_t)d * L + q0 + r] = Qs[r * AQS + d];
+        for (int e = 0; e < 8; ++e) o[tk + 16 * e] = O[i][e] * inv;
     }
 }
 
-// y[b,:,l] = mask[b,l] ? 0 : LayerNorm_over_channels(x[b,:,l]) * gamma + beta   (eps 1e-5, biased variance;
-// nn.LayerNorm(d_model) on the time-major view, then masked_fill(mask.unsqueeze(-1), 0): SubLayers.py:60,103, Layers.py:24-28)
-// block = 32 time steps x 8 channel groups
-__global__ void __launch_bounds__(256) layernorm_ncl_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                                                            const float* __restrict__ beta, const uint8_t* __restrict__ mask,
-                                                            float* __restrict__ y, int D, int L) {
-    __shared__ float red[8][33];
-    const int b = blockIdx.y, l = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5, tl = threadIdx.x & 31;
-    const bool live = l < L;
-    const float* xb = x + (size_t)b * D * L;
-    float* yb = y + (size_t)b * D * L;
-    float sum = 0.f;
-    if (live) for (int c = g; c < D; c += 8) sum += xb[(size_t)c * L + l];
-    red[g][tl] = sum;
-    __syncthreads();
-    float mean = 0.f;
+// y[r,:] = mask[r] ? 0 : LayerNorm(x[r,:]) * gamma + beta   (eps 1e-5, biased variance; nn.LayerNorm(d_model), then
+// masked_fill(mask.unsqueeze(-1), 0): SubLayers.py:60,103, Layers.py:24-28).  One warp per row, D = 32 * PER.
+template <int PER>
+__global__ void __launch_bounds__(256) layernorm_rows_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, const uint8_t* __restrict__ mask,
+                                                             float* __restrict__ y, long long rows) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    constexpr int D = 32 * PER;
+    const float* xr = x + (size_t)r * D;
+    float v[PER], sum = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) mean += red[i][tl];
-    mean *= 1.0f / D;
-    __syncthreads();
+    for (int i = 0; i < PER; ++i) { v[i] = xr[lane + 32 * i]; sum += v[i]; }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum * (1.0f / D);
     float sq = 0.f;
-    if (live) for (int c = g; c < D; c += 8) { const float d = xb[(size_t)c * L + l] - mean; sq = fmaf(d, d, sq); }
-    red[g][tl] = sq;
-    __syncthreads();
-    float var = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) var += red[i][tl];
-    const float rstd = rsqrtf(var * (1.0f / D) + 1e-5f);
-    if (!live) return;
-    const bool dead = mask && mask[(size_t)b * L + l];
-    for (int c = g; c < D; c += 8)
-        yb[(size_t)c * L + l] = dead ? 0.f : (xb[(size_t)c * L + l] - mean) * rstd * gamma[c] + beta[c];
+    for (int i = 0; i < PER; ++i) { const float d = v[i] - mean; sq = fmaf(d, d, sq); }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = rsqrtf(sq * (1.0f / D) + 1e-5f);
+    const bool dead = mask && mask[r];
+    float* yr = y + (size_t)r * D;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int c = lane + 32 * i;
+        yr[c] = dead ? 0.f : (v[i] - mean) * rstd * gamma[c] + beta[c];
+    }
 }
 
 }  // namespace
 
-int ncl_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, int B, int D, int L,
-                       cudaStream_t st) {
-    dim3 grid((unsigned)vo2w_ceil_div(L, 32), (unsigned)B);
-    layernorm_ncl_kernel<<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, D, L);
+int rows_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, long long rows, int D,
+                        cudaStream_t st) {
+    const unsigned grid = (unsigned)vo2w_ceil_div(rows, 8);
+    if (D == 256) layernorm_rows_kernel<8><<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, rows);
+    else if (D == 128) layernorm_rows_kernel<4><<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, rows);
+    else if (D == 384) layernorm_rows_kernel<12><<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, rows);
+    else if (D == 512) layernorm_rows_kernel<16><<<grid, 256, 0, st>>>(x, gamma, beta, mask, y, rows);
+    else {
+        vo2w_set_error("layernorm: width %d unsupported (128, 256, 384, 512)", D);
+        return VO2W_E_INVALID;
+    }
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
 }
 
-int ncl_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st) {
+int rows_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st) {
     VO2W_REQUIRE(D == n_head * AD, "attention: head size must be %d (d_model %d, heads %d)", AD, D, n_head);
     static bool attr_set = false;
     if (!attr_set) {
@@ -202,8 +204,9 @@ int ncl_attention(const float* qkv, const uint8_t* mask, float* out, int B, int 
 // ---------------------------------------------------------------------------------------------------------------
 struct vo2w_decoder {
     int d_model = 0, n_head = 0, d_inner = 0, k1 = 0, k2 = 0, n_layers = 0;
-    float* w_dev = nullptr;
-    struct Layer { size_t wqkv, bqkv, wfc, bfc, ln1g, ln1b, w1, b1, w2, b2, ln2g, ln2b; };
+    float* w_dev = nullptr;       // the caller's blob (biases, LayerNorm parameters are used from here)
+    float* p_dev = nullptr;       // the four weight matrices of every layer, packed for conv_tf32.cu
+    struct Layer { size_t wqkv, bqkv, wfc, bfc, ln1g, ln1b, w1, b1, w2, b2, ln2g, ln2b; size_t pqkv, pfc, p1, p2; };
     std::vector<Layer> layers;
 };
 
@@ -211,14 +214,10 @@ namespace {
 
 size_t dec_align(size_t v) { return (v + 255) / 256 * 256; }
 
-int k1conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int Cin, int Cout, int L,
-           int k, float in_slope, cudaStream_t st) {
-    SimtConv q;
-    memset(&q, 0, sizeof(q));
-    q.x = x; q.w = w; q.bias = bias; q.res = res; q.out = out;
-    q.B = B; q.Cin = Cin; q.Cout = Cout; q.L = L; q.k = k; q.dil = 1; q.pad = (k - 1) / 2; q.stride = 1;
-    q.in_slope = in_slope; q.div = 1.f;
-    return simt_conv1d(q, st);
+int conv(const float* x, const float* wp, const float* bias, const float* res, float* out, int B, int Cin, int Cout, int L, int k,
+         int act, cudaStream_t st) {
+    Tf32Conv c{x, wp, bias, res, out, B, L, Cin, Cout, k, act};
+    return tf32_conv1d(c, st);
 }
 
 }  // namespace
@@ -230,17 +229,20 @@ extern "C" int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1,
     VO2W_REQUIRE(blob_host && out, "decoder_create: null argument");
     VO2W_REQUIRE(d_model > 0 && n_head > 0 && d_model == n_head * AD, "decoder_create: d_model %d / heads %d: head size must be %d",
                  d_model, n_head, AD);
-    VO2W_REQUIRE(d_inner > 0 && n_layers > 0 && (k1 & 1) && (k2 & 1) && k1 >= 1 && k1 <= 11 && k2 >= 1 && k2 <= 11,
-                 "decoder_create: bad shape (d_inner %d, kernels %d/%d, layers %d)", d_inner, k1, k2, n_layers);
+    VO2W_REQUIRE(d_inner > 0 && n_layers > 0 && tf32_conv_supported(d_inner, d_model, k1) && tf32_conv_supported(d_model, d_inner, k2),
+                 "decoder_create: unsupported shape (d_inner %d must be a multiple of 64, odd kernels <= 11: %d/%d, layers %d)",
+                 d_inner, k1, k2, n_layers);
     int rc = vo2w_device_check();
     if (rc != VO2W_OK) return rc;
     vo2w_decoder* d = new vo2w_decoder();
     d->d_model = d_model; d->n_head = n_head; d->d_inner = d_inner; d->k1 = k1; d->k2 = k2; d->n_layers = n_layers;
     const size_t D = (size_t)d_model, H = (size_t)d_inner;
-    size_t off = 0;
+    size_t off = 0, poff = 0;
     auto take = [&](size_t n) { const size_t o = off; off += n; return o; };
+    auto ptake = [&](size_t n) { const size_t o = poff; poff += 2 * n; return o; };
     for (int i = 0; i < n_layers; ++i) {
         vo2w_decoder::Layer l;
+        l.pqkv = ptake(3 * D * D); l.pfc = ptake(D * D); l.p1 = ptake(H * D * k1); l.p2 = ptake(D * H * k2);
         l.wqkv = take(3 * D * D); l.bqkv = take(3 * D);
         l.wfc = take(D * D); l.bfc = take(D);
         l.ln1g = take(D); l.ln1b = take(D);
@@ -254,11 +256,24 @@ extern "C" int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1,
         delete d;
         return VO2W_E_INVALID;
     }
-    if (cudaMalloc(&d->w_dev, n_floats * 4) != cudaSuccess ||
+    if (cudaMalloc(&d->w_dev, n_floats * 4) != cudaSuccess || cudaMalloc(&d->p_dev, poff * 4) != cudaSuccess ||
         cudaMemcpy(d->w_dev, blob_host, n_floats * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
         vo2w_set_error("decoder_create: uploading weights failed");
-        if (d->w_dev) cudaFree(d->w_dev);
-        delete d;
+        vo2w_decoder_destroy(d);
+        return VO2W_E_CUDA;
+    }
+    for (const auto& l : d->layers) {
+        if ((rc = tf32_conv_pack(d->w_dev + l.wqkv, 3 * d_model, d_model, 1, d->p_dev + l.pqkv, 0)) != VO2W_OK ||
+            (rc = tf32_conv_pack(d->w_dev + l.wfc, d_model, d_model, 1, d->p_dev + l.pfc, 0)) != VO2W_OK ||
+            (rc = tf32_conv_pack(d->w_dev + l.w1, d_inner, d_model, k1, d->p_dev + l.p1, 0)) != VO2W_OK ||
+            (rc = tf32_conv_pack(d->w_dev + l.w2, d_model, d_inner, k2, d->p_dev + l.p2, 0)) != VO2W_OK) {
+            vo2w_decoder_destroy(d);
+            return rc;
+        }
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess) {
+        vo2w_set_error("decoder_create: packing weights failed");
+        vo2w_decoder_destroy(d);
         return VO2W_E_CUDA;
     }
     *out = d;
@@ -268,6 +283,7 @@ extern "C" int vo2w_decoder_create(int d_model, int n_head, int d_inner, int k1,
 extern "C" int vo2w_decoder_destroy(vo2w_decoder* d) {
     if (!d) return VO2W_OK;
     if (d->w_dev) cudaFree(d->w_dev);
+    if (d->p_dev) cudaFree(d->p_dev);
     delete d;
     return VO2W_OK;
 }
@@ -293,27 +309,29 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
     const int D = d->d_model, H = d->d_inner;
     const size_t bl = (size_t)B * L * 4;
     uint8_t* ws = (uint8_t*)workspace;
-    float* cur = (float*)ws;                                   // [B,D,L] layer input / output
-    float* tmp = (float*)(ws + dec_align(bl * D));             // [B,D,L] pre-LayerNorm sums
-    float* qkv = (float*)(ws + 2 * dec_align(bl * D));         // [B,3D,L]
-    float* hid = (float*)(ws + 2 * dec_align(bl * D) + dec_align(bl * 3 * D));   // [B,d_inner,L]; first holds the attention output
+    float* cur = (float*)ws;                                   // [B,L,D] layer input / output
+    float* tmp = (float*)(ws + dec_align(bl * D));             // [B,L,D] pre-LayerNorm sums
+    float* qkv = (float*)(ws + 2 * dec_align(bl * D));         // [B,L,3D]
+    float* hid = (float*)(ws + 2 * dec_align(bl * D) + dec_align(bl * 3 * D));   // [B,L,d_inner]; first holds the attention output
+    const long long rows = (long long)B * L;
 
-    // enc_seq + position_enc[:, :L]  (Models.py:184-186), then channel-major for the whole stack
-    int rc = rows_add_table(x, pos, tmp, B, L, D, st);
-    if (rc != VO2W_OK) return rc;
-    rc = rows_transpose_add(tmp, nullptr, cur, B, L, D, st);
+    // enc_seq + position_enc[:, :L]  (Models.py:184-186)
+    int rc = rows_add_table(x, pos, cur, B, L, D, st);
     if (rc != VO2W_OK) return rc;
     const float* W = d->w_dev;
-    for (const auto& l : d->layers) {
+    const float* P = d->p_dev;
+    for (size_t i = 0; i < d->layers.size(); ++i) {
+        const auto& l = d->layers[i];
+        float* dst = i + 1 == d->layers.size() ? out : cur;
         // MultiHeadAttention (SubLayers.py:31-62)
-        if ((rc = k1conv(cur, W + l.wqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 1.f, st)) != VO2W_OK) return rc;
-        if ((rc = ncl_attention(qkv, mask, hid, B, L, D, d->n_head, st)) != VO2W_OK) return rc;
-        if ((rc = k1conv(hid, W + l.wfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 1.f, st)) != VO2W_OK) return rc;
-        if ((rc = ncl_layernorm_mask(tmp, W + l.ln1g, W + l.ln1b, mask, cur, B, D, L, st)) != VO2W_OK) return rc;
-        // PositionwiseFeedForward (SubLayers.py:95-104); relu rides the second convolution's staging (slope 0)
-        if ((rc = k1conv(cur, W + l.w1, W + l.b1, nullptr, hid, B, D, H, L, d->k1, 1.f, st)) != VO2W_OK) return rc;
-        if ((rc = k1conv(hid, W + l.w2, W + l.b2, cur, tmp, B, H, D, L, d->k2, 0.f, st)) != VO2W_OK) return rc;
-        if ((rc = ncl_layernorm_mask(tmp, W + l.ln2g, W + l.ln2b, mask, cur, B, D, L, st)) != VO2W_OK) return rc;
+        if ((rc = conv(cur, P + l.pqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 0, st)) != VO2W_OK) return rc;
+        if ((rc = rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)) != VO2W_OK) return rc;
+        if ((rc = conv(hid, P + l.pfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 0, st)) != VO2W_OK) return rc;
+        if ((rc = rows_layernorm_mask(tmp, W + l.ln1g, W + l.ln1b, mask, cur, rows, D, st)) != VO2W_OK) return rc;
+        // PositionwiseFeedForward (SubLayers.py:95-104); relu rides the first convolution's epilogue
+        if ((rc = conv(cur, P + l.p1, W + l.b1, nullptr, hid, B, D, H, L, d->k1, 1, st)) != VO2W_OK) return rc;
+        if ((rc = conv(hid, P + l.p2, W + l.b2, cur, tmp, B, H, D, L, d->k2, 0, st)) != VO2W_OK) return rc;
+        if ((rc = rows_layernorm_mask(tmp, W + l.ln2g, W + l.ln2b, mask, dst, rows, D, st)) != VO2W_OK) return rc;
     }
-    return rows_transpose_add(cur, nullptr, out, B, D, L, st);
+    return VO2W_OK;
 }

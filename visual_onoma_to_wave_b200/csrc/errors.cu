@@ -19,10 +19,13 @@ extern "C" int vo2w_device_check(void) {
         vo2w_set_error("no CUDA device");
         return VO2W_E_NODEVICE;
     }
-    cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10) {
+    static int checked[64];                       // cudaGetDeviceProperties costs milliseconds: ask once per device
+    if (dev >= 0 && dev < 64 && checked[dev]) return VO2W_OK;
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess || major != 10) {
         vo2w_set_error("device is not sm_100 (compute capability 10.x)");
         return VO2W_E_NODEVICE;
     }
+    if (dev >= 0 && dev < 64) checked[dev] = 1;
     return VO2W_OK;
 }

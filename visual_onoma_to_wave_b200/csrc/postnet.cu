@@ -6,18 +6,21 @@
 //   vTTS.forward (scripts/model/vtts.py:106-107):  output = mel_linear(output); postnet_output = postnet(output) + output
 //
 // BatchNorm (eval) is an affine map per channel, folded into the convolution's weight and bias by the caller
-// (postnet.py), as weight_norm is for the vocoder.  fp32 CUDA-core path: the layers are 8.7 MFLOP per frame, 1.4 % of
-// the vocoder's 614 MFLOP, so they ride the exact-mode convolution kernel (conv_simt.cu) between two tiled
-// transposes; the second transpose fuses the `+ output` of vtts.py:107 on request.
+// (postnet.py), as weight_norm is for the vocoder.  The convolutions run time-major on the tensor pipe with fp32-level
+// accuracy (conv_tf32.cu: kind::tf32 with a hi/lo operand split): no transposes, tanh and the `+ output` of
+// vtts.py:107 ride the epilogues.  Shapes the tensor-pipe kernel does not tile (channel counts that are not multiples
+// of 8 / 16) fall back to the fp32 CUDA-core kernel (conv_simt.cu) between two tiled transposes.
 #include <vector>
 
 #include "conv_simt.cuh"
+#include "conv_tf32.cuh"
 #include "rows.cuh"
 
 struct vo2w_postnet {
     int n_mel = 0, dim = 0, k = 0, n_conv = 0;
     float* w_dev = nullptr;
-    std::vector<size_t> w_off, b_off;
+    float* p_dev = nullptr;       // packed for conv_tf32.cu (null: CUDA-core fallback)
+    std::vector<size_t> w_off, b_off, p_off;
 };
 
 namespace {
@@ -55,6 +58,33 @@ extern "C" int vo2w_postnet_create(int n_mel, int dim, int k, int n_conv, const 
         delete p;
         return VO2W_E_CUDA;
     }
+    bool tensor = true;
+    size_t poff = 0;
+    for (int i = 0; i < n_conv; ++i) {
+        const int cin = i == 0 ? n_mel : dim, cout = i == n_conv - 1 ? n_mel : dim;
+        tensor = tensor && tf32_conv_supported(cout, cin, k);
+        p->p_off.push_back(poff);
+        poff += tf32_conv_packed_floats(cout, cin, k);
+    }
+    if (tensor) {
+        if (cudaMalloc(&p->p_dev, poff * 4) != cudaSuccess) {
+            vo2w_set_error("postnet_create: allocating packed weights failed");
+            vo2w_postnet_destroy(p);
+            return VO2W_E_CUDA;
+        }
+        for (int i = 0; i < n_conv; ++i) {
+            const int cin = i == 0 ? n_mel : dim, cout = i == n_conv - 1 ? n_mel : dim;
+            if ((rc = tf32_conv_pack(p->w_dev + p->w_off[i], cout, cin, k, p->p_dev + p->p_off[i], 0)) != VO2W_OK) {
+                vo2w_postnet_destroy(p);
+                return rc;
+            }
+        }
+        if (cudaDeviceSynchronize() != cudaSuccess) {
+            vo2w_set_error("postnet_create: packing weights failed");
+            vo2w_postnet_destroy(p);
+            return VO2W_E_CUDA;
+        }
+    }
     *out = p;
     return VO2W_OK;
 }
@@ -62,6 +92,7 @@ extern "C" int vo2w_postnet_create(int n_mel, int dim, int k, int n_conv, const 
 extern "C" int vo2w_postnet_destroy(vo2w_postnet* p) {
     if (!p) return VO2W_OK;
     if (p->w_dev) cudaFree(p->w_dev);
+    if (p->p_dev) cudaFree(p->p_dev);
     delete p;
     return VO2W_OK;
 }
@@ -82,6 +113,22 @@ extern "C" int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int 
     }
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t* ws = (uint8_t*)workspace;
+    if (p->p_dev) {
+        // time-major all the way: [B,L,n_mel] -> tanh(conv) x (n_conv - 1) -> conv (+ x)
+        float* buf[2] = {(float*)(ws + align256((size_t)B * p->n_mel * L * 4)),
+                         (float*)(ws + align256((size_t)B * p->n_mel * L * 4) + align256((size_t)B * p->dim * L * 4))};
+        const float* cur = x;
+        for (int i = 0; i < p->n_conv; ++i) {
+            const bool last = i == p->n_conv - 1;
+            Tf32Conv c{cur, p->p_dev + p->p_off[i], p->w_dev + p->b_off[i], (last && add_input) ? x : nullptr,
+                       last ? out : buf[i & 1], B, L, i == 0 ? p->n_mel : p->dim, last ? p->n_mel : p->dim, p->k,
+                       last ? 0 : 2};           // torch.tanh on all but the last convolution (Layers.py:129-131)
+            const int rc = tf32_conv1d(c, st);
+            if (rc != VO2W_OK) return rc;
+            cur = c.out;
+        }
+        return VO2W_OK;
+    }
     float* x_ncl = (float*)ws;
     float* buf[2] = {(float*)(ws + align256((size_t)B * p->n_mel * L * 4)),
                      (float*)(ws + align256((size_t)B * p->n_mel * L * 4) + align256((size_t)B * p->dim * L * 4))};
@@ -108,7 +155,15 @@ extern "C" int vo2w_postnet_forward(vo2w_postnet* p, const float* x, int B, int 
 }
 
 extern "C" int vo2w_linear_forward(const float* x, const float* w, const float* bias, long long rows, int K, int N, float* y,
-                                   void* stream) {
+                                   float* scratch, void* stream) {
     VO2W_REQUIRE(x && w && y, "linear_forward: null argument");
-    return rows_linear(x, w, bias, rows, K, N, y, (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (scratch && rows > 0 && rows < (1ll << 31) && tf32_conv_supported(N, K, 1) && ((uintptr_t)bias & 15) == 0) {
+        // a k=1 convolution over one "utterance" of `rows` frames on the tensor pipe (fp32-level accuracy)
+        const int rc = tf32_conv_pack(w, N, K, 1, scratch, st);
+        if (rc != VO2W_OK) return rc;
+        Tf32Conv c{x, scratch, bias, nullptr, y, 1, (int)rows, K, N, 1, 0};
+        return tf32_conv1d(c, st);
+    }
+    return rows_linear(x, w, bias, rows, K, N, y, st);
 }

@@ -9,7 +9,9 @@ int rows_transpose_add(const float* in, const float* add, float* out, int B, int
 int rows_linear(const float* x, const float* w, const float* bias, long long rows, int K, int N, float* y, cudaStream_t st);
 // y[b,l,:] = x[b,l,:] + table[l,:]
 int rows_add_table(const float* x, const float* table, float* y, int B, int L, int D, cudaStream_t st);
-// channel-major [B,D,L] pieces of the FFT blocks (decoder.cu)
-int ncl_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, int B, int D, int L,
-                       cudaStream_t st);
-int ncl_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st);
+// time-major pieces of the FFT blocks (decoder.cu)
+// y[r,:] = mask[r] ? 0 : LayerNorm(x[r,:]) * gamma + beta
+int rows_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, long long rows, int D,
+                        cudaStream_t st);
+// qkv [B*L][3D] -> out [B*L][D]: softmax(q k^T / sqrt(128), key padding mask) v per head of 128 columns
+int rows_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st);

@@ -138,10 +138,10 @@ class Decoder(nn.Module):
         self._drop_handle()
         self._pos = None
 
-    def load_state_dict(self, *a, **kw):
-        r = super().load_state_dict(*a, **kw)
+    def _load_from_state_dict(self, *a, **kw):
+        # runs for direct and for parent-driven loads alike: the device copy of the weights is stale afterwards
+        super()._load_from_state_dict(*a, **kw)
         self.refresh()
-        return r
 
     def _get_handle(self, device):
         if self._handle is not None and self._handle_dev == device:

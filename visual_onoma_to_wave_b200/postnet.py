@@ -94,10 +94,10 @@ class PostNet(nn.Module):
         """Re-fold the weights on the next forward (after load_state_dict / in-place edits)."""
         self._drop_handle()
 
-    def load_state_dict(self, *a, **kw):
-        r = super().load_state_dict(*a, **kw)
-        self._drop_handle()
-        return r
+    def _load_from_state_dict(self, *a, **kw):
+        # runs for direct and for parent-driven loads alike: the device copy of the weights is stale afterwards
+        super()._load_from_state_dict(*a, **kw)
+        self.refresh()
 
     def _get_handle(self, device):
         if self._handle is not None and self._handle_dev == device:
@@ -135,7 +135,9 @@ def mel_linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None 
     y = torch.empty(x2.shape[0], N, dtype=torch.float32, device=x.device)
     if x2.shape[0]:
         with torch.cuda.device(x.device):
+            scratch = torch.empty(2 * N * K, dtype=torch.float32, device=x.device)     # packed weights (tensor-pipe path)
             stream = torch.cuda.current_stream(x.device).cuda_stream
             _lib.check(_lib.lib().vo2w_linear_forward(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None,
-                                                      x2.shape[0], K, N, y.data_ptr(), stream), "vo2w_linear_forward")
+                                                      x2.shape[0], K, N, y.data_ptr(), scratch.data_ptr(), stream),
+                       "vo2w_linear_forward")
     return y.reshape(*x.shape[:-1], N)

@@ -101,6 +101,11 @@ class VariancePredictor(nn.Module):
     def refresh(self):
         self._drop_handle()
 
+    def _load_from_state_dict(self, *a, **kw):
+        # runs for direct and for parent-driven loads alike: the device copy of the weights is stale afterwards
+        super()._load_from_state_dict(*a, **kw)
+        self.refresh()
+
     def _get_handle(self, device):
         if self._handle is not None and self._handle_dev == device:
             return self._handle
