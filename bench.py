@@ -13,6 +13,7 @@ sub-batches.  One JSON line on rank 0.
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 import sys
@@ -187,7 +188,8 @@ def run_ours(args):
     sub = min(args.sub_batch, n_local)
     gen = v.Generator(v.AttrDict(V1_CONFIG), precision=args.precision)
     gen.eval()
-    gen.remove_weight_norm()
+    with contextlib.redirect_stdout(sys.stderr):     # the reference prints here; stdout carries the JSON line only
+        gen.remove_weight_norm()
     gen.load_state_dict(seeded_state_dict(1234))
     gen.to(dev)
     gen.host_sub_batch = sub
@@ -285,6 +287,14 @@ def run_ours(args):
             extra["length_regulator"] = lr_bandwidth(dev, peaks)
         except Exception as e:  # reported, not fatal for the vocoder metric
             extra["length_regulator"] = {"error": str(e)}
+        if world == 1:
+            try:   # the acoustic tail in front of the vocoder, device timing per stage
+                sys.path.insert(0, os.path.join(ROOT, "tools"))
+                import bench_tail
+                with torch.cuda.device(dev), contextlib.redirect_stdout(sys.stderr):
+                    extra["acoustic_tail"] = bench_tail.measure(steps=3, warmup=2, batch=64, dev=dev)
+            except Exception as e:
+                extra["acoustic_tail"] = {"error": str(e)}
         if world == 1 and not args.no_cpu_baseline:
             n_cpu = 64
             audio_s, times = cpu_generator_rate(n_cpu, reps=2, warm=1)

@@ -16,8 +16,8 @@
 // per row), exactly as in the bf16 vocoder kernels.  Weights are packed once (tf32_conv_pack) in consumption order
 // and streamed by cp.async.bulk through an mbarrier ring; NB row blocks share every weight stage.
 //
-// Warp roles (320 threads): warps 0-7 stage the activation chunks (two groups of four, alternating chunks, so two
-// global loads are in flight) and later run the epilogue; warp 8 streams the weights; warp 9 owns TMEM and issues
+// Warp roles (320 threads): warps 0-7 stage the activation chunks (two groups of four, alternating chunk pairs, so
+// four chunk loads are in flight) and later run the epilogue; warp 8 streams the weights; warp 9 owns TMEM and issues
 // the MMAs from one elected thread.
 #include "conv_tf32.cuh"
 
@@ -98,50 +98,45 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
 
     if (warp < 8) {
         // ===================== activation producers: global fp32 -> hi/lo core matrices =====================
-        const int g = warp >> 2, tg = threadIdx.x & 127;
-        constexpr int NR = NB + 1;                       // rows per thread: NB*128 + halo <= (NB+1)*128
+        // Each group of four warps takes chunks in pairs (group 0: 0,1,4,5,..; group 1: 2,3,6,7,..).  A pair is 64
+        // contiguous bytes per frame: lane = (16-byte segment, row) so that one warp load touches 8 rows x 64 B (8 cache
+        // lines, not 32) and one quarter-warp store phase writes 128 contiguous bytes of one k-column.
+        const int g = warp >> 2, wq = warp & 3, seg = lane >> 3, r_in = wq * 8 + (lane & 7);
+        constexpr int NRI = NB * 4 + 1;                  // row iterations: (NB*128 + halo, rounded to 8) / 32 rows per pass
         const float* xb = p.c.x + (size_t)b * L * Cin;
-        // each group takes chunks in pairs (group 0: 0,1,4,5,..; group 1: 2,3,6,7,..): four chunk loads in flight
         for (int c0 = 2 * g; c0 < p.chunks; c0 += 4) {
-            float4 v[2][NR][2];
+            const bool pair = c0 + 1 < p.chunks;
+            const bool mine = seg < 2 || pair;            // segments 2, 3 belong to the second chunk of the pair
+            float4 v[NRI];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-#pragma unroll
-                for (int i = 0; i < NR; ++i) {
-                    const int r = tg + 128 * i, l = l0 - pad + r;
-                    if (c0 + u < p.chunks && r < p.R && l >= 0 && l < L) {
-                        const float4* src = reinterpret_cast<const float4*>(xb + (size_t)l * Cin + (c0 + u) * T32_KC);
-                        v[u][i][0] = __ldg(src);
-                        v[u][i][1] = __ldg(src + 1);
-                    } else {
-                        v[u][i][0] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        v[u][i][1] = v[u][i][0];
-                    }
-                }
+            for (int i = 0; i < NRI; ++i) {
+                const int r = i * 32 + r_in, l = l0 - pad + r;
+                if (mine && r < p.R && l >= 0 && l < L)
+                    v[i] = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * Cin + c0 * T32_KC) + seg);
+                else
+                    v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
+            const int s0 = c0 % T32_AS, s1 = (c0 + 1) % T32_AS, use = c0 / T32_AS;      // c0 is even: same `use` for both
+            if (use > 0) {
+                mbar_wait(a_empty(s0), (uint32_t)((use - 1) & 1));
+                if (pair) mbar_wait(a_empty(s1), (uint32_t)((use - 1) & 1));
+            }
+            if (mine) {
+                const uint32_t base = a_ring + (uint32_t)(seg < 2 ? s0 : s1) * p.a_stage_bytes + (uint32_t)((seg & 1) * R8) * 16u;
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                const int c = c0 + u;
-                if (c >= p.chunks) break;
-                const int s = c % T32_AS, use = c / T32_AS;
-                if (use > 0) mbar_wait(a_empty(s), (uint32_t)((use - 1) & 1));
-                const uint32_t base = a_ring + (uint32_t)s * p.a_stage_bytes;
-#pragma unroll
-                for (int i = 0; i < NR; ++i) {
-                    const int r = tg + 128 * i;
+                for (int i = 0; i < NRI; ++i) {
+                    const int r = i * 32 + r_in;
                     if (r < R8) {
                         float4 hi, lo;
-                        split4(v[u][i][0], hi, lo);
+                        split4(v[i], hi, lo);
                         st_shared_f4(base + (uint32_t)r * 16u, hi);
                         st_shared_f4(base + (uint32_t)(2 * R8 + r) * 16u, lo);
-                        split4(v[u][i][1], hi, lo);
-                        st_shared_f4(base + (uint32_t)(R8 + r) * 16u, hi);
-                        st_shared_f4(base + (uint32_t)(3 * R8 + r) * 16u, lo);
                     }
                 }
-                fence_proxy_async();                      // generic-proxy stores -> visible to the tensor pipe
-                mbar_arrive(a_full(s));
             }
+            fence_proxy_async();                          // generic-proxy stores -> visible to the tensor pipe
+            mbar_arrive(a_full(s0));
+            if (pair) mbar_arrive(a_full(s1));
         }
 
         // ===================== epilogue: TMEM -> bias / residual / activation -> global =====================
