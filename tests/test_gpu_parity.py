@@ -319,7 +319,7 @@ def test_host_pipeline_matches_single_call(dev, gens):
 # ------------------------------------------------------------------------------------------
 # PostNet + mel_linear
 # ------------------------------------------------------------------------------------------
-POSTNET_TOL = 1e-4     # max-abs-err of the fp32 path against the reference's fp32 CPU output (values reach +-5.5)
+POSTNET_TOL = 2e-4   # outputs reach +-8: 2.5e-5 of full scale; measured <= 9.5e-5 (tensor-pipe accumulation)
 
 
 @pytest.mark.gpu

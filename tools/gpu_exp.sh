@@ -1,29 +1,31 @@
 #!/bin/bash
 # scratch experiment script (GPU box)
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_parity.py -q -m gpu -k "tf32 or decoder or acoustic or postnet" 2>&1 | grep -E "AssertionError: |passed|failed|^FAILED|Error" | head -30 > gpurun_out/exp_tests.log
-cat gpurun_out/exp_tests.log
-timeout 300 python __graft_entry__.py --smoke 2>&1 | tail -2
-timeout 300 python - > gpurun_out/exp_tf32.log 2>&1 <<'PY'
-import torch
-from visual_onoma_to_wave_b200 import _lib
-dev = torch.device("cuda:0")
-lib = _lib.lib()
-for (B, L, Cin, Cout, k) in ((64, 479, 256, 1024, 9), (64, 479, 1024, 256, 1), (64, 479, 256, 768, 1), (64, 479, 256, 256, 1), (64, 479, 512, 512, 5), (64, 479, 256, 80, 1)):
-    x = torch.randn(B, L, Cin, device=dev); w = torch.randn(Cout, Cin, k, device=dev) * 0.05; b = torch.randn(Cout, device=dev)
-    out = torch.empty(B, L, Cout, device=dev); scratch = torch.empty(2 * w.numel(), device=dev)
-    st = torch.cuda.current_stream().cuda_stream
-    def run(): _lib.check(lib.vo2w_debug_tf32_conv(x.data_ptr(), w.data_ptr(), b.data_ptr(), None, out.data_ptr(), B, L, Cin, Cout, k, 0, scratch.data_ptr(), st))
-    for _ in range(2): run()
-    torch.cuda.synchronize(); e0 = torch.cuda.Event(True); e1 = torch.cuda.Event(True); e0.record()
-    for _ in range(5): run()
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 5
-    fl = 2 * B * L * Cin * Cout * k
-    print(f"B{B} L{L} {Cin}->{Cout} k{k}: {ms*1e3:.0f} us (incl. pack)  {fl/ms/1e9:.1f} TFLOP/s fp32-equivalent, {3*fl/ms/1e9:.0f} TF32 TFLOP/s")
+timeout 300 python - > gpurun_out/exp_err.log 2>&1 <<'PY'
+import torch, numpy as np
+import visual_onoma_to_wave_b200 as v
+from visual_onoma_to_wave_b200.synthetic import seeded_postnet_state_dict, seeded_decoder_state_dict, decoder_config
+from oracle import postnet_oracle as po, decoder_oracle as do
+g = np.load("tests/golden/postnet.npz")
+pn = v.PostNet(); pn.load_state_dict(seeded_postnet_state_dict(4321)); pn.eval().cuda()
+for name in "abc":
+    x = torch.from_numpy(g[f"x_{name}"]).cuda(); ref = torch.from_numpy(g[f"y_{name}"])
+    print("postnet golden", name, float((pn(x).cpu() - ref).abs().max()), "ref max", float(ref.abs().max()))
+sd = seeded_postnet_state_dict(99); pn = v.PostNet(); pn.load_state_dict(sd); pn.eval().cuda()
+x = torch.randn(64, 490, 80, generator=torch.Generator().manual_seed(5)) * 2 - 3
+ref = po.postnet_forward(sd, x); got = pn(x.cuda()).cpu()
+print("postnet cfg3", float((got - ref).abs().max()), "ref max", float(ref.abs().max()), "rms err", float((got-ref).pow(2).mean().sqrt()))
+# fp64 arbiter: how far is the fp32 CPU oracle itself from fp64?
+sd64 = {k: (t.double() if t.is_floating_point() else t) for k, t in sd.items()}
+ref64 = po.postnet_forward(sd64, x.double())
+print("  oracle fp32 vs fp64", float((ref.double() - ref64).abs().max()), " gpu vs fp64", float((got.double() - ref64).abs().max()))
+kw = dict(n_layers=6); sdd = seeded_decoder_state_dict(5, **kw)
+dec = v.Decoder(decoder_config(**kw)); dec.load_state_dict(sdd); dec.eval().cuda()
+lens = torch.tensor([490, 257, 64, 65, 1, 128, 300, 33]); L = 490
+x = torch.randn(8, L, 256, generator=torch.Generator().manual_seed(3)); mask = torch.arange(L)[None, :] >= lens[:, None]
+ref, _ = do.decoder_forward(sdd, x, mask); got, _ = dec(x.cuda(), mask.cuda())
+sd64 = {k: t.double() for k, t in sdd.items()}
+ref64, _ = do.decoder_forward(sd64, x.double(), mask)
+print("decoder 6 layers ragged", float((got.cpu() - ref).abs().max()), "oracle fp32 vs fp64", float((ref.double() - ref64).abs().max()), "gpu vs fp64", float((got.cpu().double() - ref64).abs().max()))
 PY
-cat gpurun_out/exp_tf32.log
-python tools/bench_tail.py 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read())
-print({k:round(v['ms'],2) for k,v in d['stages'].items()}, 'chain', round(d['chain_ms'],2))"
+cat gpurun_out/exp_err.log
