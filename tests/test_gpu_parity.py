@@ -319,7 +319,7 @@ def test_host_pipeline_matches_single_call(dev, gens):
 # ------------------------------------------------------------------------------------------
 # PostNet + mel_linear
 # ------------------------------------------------------------------------------------------
-POSTNET_TOL = 2e-4   # outputs reach +-8: 2.5e-5 of full scale; measured <= 9.5e-5 (tensor-pipe accumulation)
+POSTNET_TOL = 1e-4     # max-abs-err against the reference's fp32 CPU output (values reach +-8; measured <= 5.4e-5)
 
 
 @pytest.mark.gpu
@@ -566,8 +566,8 @@ TF32_SHAPES = [  # B, L, Cin, Cout, k, act, res      (the acoustic tail's layers
 @pytest.mark.parametrize("shape", TF32_SHAPES)
 def test_tf32_split_convolution_is_fp32_accurate(dev, shape):
     """tcgen05 kind::tf32 with the hi/lo operand split against an fp64 convolution.  A single-pass TF32 product is
-    ~1e-3 off here; the split leaves the tensor pipe's truncating fp32 accumulation, ~1e-7 per accumulation of the
-    hi.hi chain (K/8 of them): 3e-5 max-abs at K = 2304 on O(1) outputs, 5e-6 at K = 256."""
+    ~1e-3 off here; the split leaves the tensor pipe's truncating fp32 accumulation, whose mean the epilogue
+    compensates (conv_tf32.cu): 1.2e-5 max-abs at K = 2304 on O(1) outputs, 2e-6 at K = 256."""
     import torch.nn.functional as F
     B, L, Cin, Cout, k, act, use_res = shape
     g = torch.Generator().manual_seed(Cin * 7 + Cout + k)
@@ -588,7 +588,7 @@ def test_tf32_split_convolution_is_fp32_accurate(dev, shape):
                                                    out.data_ptr(), B, L, Cin, Cout, k, act, scratch.data_ptr(),
                                                    torch.cuda.current_stream(dev).cuda_stream), "vo2w_debug_tf32_conv")
     err = float((out.cpu().double() - ref).abs().max())
-    assert err <= 4e-6 + 2e-8 * Cin * k, err
+    assert err <= 4e-6 + 1e-8 * Cin * k, err
 
 
 def test_error_conventions(dev, gens):

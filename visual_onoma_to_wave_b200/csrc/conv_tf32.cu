@@ -8,6 +8,10 @@
 // a bias that grows with the number of accumulations (measured 8.6e-5 max-abs at K = 2304 with one accumulator), so
 // the hi.hi chain and the two small-term chains get SEPARATE TMEM accumulators (the small chain's truncation is
 // 2^-11 of the main one's) that the epilogue adds in registers: a third of the accumulations at full magnitude.
+// What remains is a shrink of the main accumulator that is linear in its number of accumulations n = Cin*k/8:
+// measured -1.63e-8 * n (+- 2 %, n = 8..384) for zero-mean products, -5.3e-8 * n for same-sign products
+// (profiles/r01_tf32_accumulation_bias.txt).  The epilogue multiplies the main accumulator by (1 + 1.63e-8 * n),
+// which removes the mean of the error for activations-times-weights data: 3.5e-5 -> 1.3e-5 max-abs at n = 320.
 //
 // Geometry: activations are time-major [B,L,C]; one CTA owns NB blocks of 128 consecutive frames of one utterance x
 // one tile of n_t output channels (accumulators: 2 x NB x n_t TMEM columns).  Input channels are walked in chunks of 8
@@ -27,6 +31,7 @@ constexpr int T32_THREADS = 320;
 constexpr int T32_AS = 4;        // activation stages
 constexpr int T32_WS = 8;        // weight stages
 constexpr int T32_KC = 8;        // input channels per chunk (one kind::tf32 k-step)
+constexpr float T32_TRUNC_PER_ACC = 1.63e-8f;     // measured relative loss of the truncating accumulator per accumulation
 
 struct T32K {
     Tf32Conv c;
@@ -145,6 +150,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         const int q = warp & 3, h = warp >> 2, m = q * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const int co0 = tile * n_t;
+        const float comp = 1.0f + T32_TRUNC_PER_ACC * (float)(p.chunks * k);
 #pragma unroll 1
         for (int blk = 0; blk < NB; ++blk) {
             const int l = l0 + blk * 128 + m;
@@ -162,8 +168,8 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
                 float y[16];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    y[i] = __uint_as_float(r0[i]) + __uint_as_float(s0[i]);
-                    y[8 + i] = __uint_as_float(r1[i]) + __uint_as_float(s1[i]);
+                    y[i] = fmaf(__uint_as_float(r0[i]), comp, __uint_as_float(s0[i]));
+                    y[8 + i] = fmaf(__uint_as_float(r1[i]), comp, __uint_as_float(s1[i]));
                 }
                 if (p.c.bias) {
                     const float4* bp = reinterpret_cast<const float4*>(p.c.bias + co0 + cc * 16);
