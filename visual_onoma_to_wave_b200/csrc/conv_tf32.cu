@@ -77,8 +77,9 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int l0 = blockIdx.x * 128 * NB, tile = blockIdx.y, b = blockIdx.z;
-    const int k = p.c.k, pad = (k - 1) / 2, L = p.c.L, Cin = p.c.Cin, n_t = p.n_t, R8 = p.R8;
+    const int l0 = blockIdx.x * 128 * NB, tile = blockIdx.y;
+    const int b = (int)blockIdx.z / p.c.heads, zh = (int)blockIdx.z % p.c.heads;          // heads >= 1 (host)
+    const int k = p.c.k, pad = (k - 1) / 2, L = p.c.L, ldx = p.c.ldx, n_t = p.n_t, R8 = p.R8;
 
     const uint32_t a_ring = smem_u32(smem);
     const uint32_t w_ring = a_ring + T32_AS * p.a_stage_bytes;
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         // lines, not 32) and one quarter-warp store phase writes 128 contiguous bytes of one k-column.
         const int g = warp >> 2, wq = warp & 3, seg = lane >> 3, r_in = wq * 8 + (lane & 7);
         constexpr int NRI = NB * 4 + 1;                  // row iterations: (NB*128 + halo, rounded to 8) / 32 rows per pass
-        const float* xb = p.c.x + (size_t)b * L * Cin;
+        const float* xb = p.c.x + (size_t)b * L * ldx + (size_t)zh * p.c.x_hs;
         for (int c0 = 2 * g; c0 < p.chunks; c0 += 4) {
             const bool pair = c0 + 1 < p.chunks;
             const bool mine = seg < 2 || pair;            // segments 2, 3 belong to the second chunk of the pair
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
             for (int i = 0; i < NRI; ++i) {
                 const int r = i * 32 + r_in, l = l0 - pad + r;
                 if (mine && r < p.R && l >= 0 && l < L)
-                    v[i] = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * Cin + c0 * T32_KC) + seg);
+                    v[i] = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * ldx + c0 * T32_KC) + seg);
                 else
                     v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         for (int blk = 0; blk < NB; ++blk) {
             const int l = l0 + blk * 128 + m;
             const bool live = l < L;
-            const size_t row = ((size_t)b * L + (live ? l : 0)) * p.c.Cout + co0;
+            const size_t row = ((size_t)b * L + (live ? l : 0)) * p.c.ldo + (size_t)zh * p.c.o_hs + co0;
 #pragma unroll 1
             for (int cc = h; cc < n_t / 16; cc += 2) {
                 uint32_t r0[8], r1[8], s0[8], s1[8];
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         // ===================== weight producer: packed stages through the bulk-copy engine =====================
         if (lane == 0) {
             const int n_it = p.chunks * k;
-            const float* src = p.c.wp + (size_t)tile * n_it * (p.w_stage_bytes / 4);
+            const float* src = p.c.wp + (size_t)blockIdx.z * p.c.w_zs + (size_t)tile * n_it * (p.w_stage_bytes / 4);
             for (int it = 0; it < n_it; ++it) {
                 const int s = it % T32_WS;
                 if (it >= T32_WS) mbar_wait(w_empty(s), (uint32_t)((it / T32_WS - 1) & 1));
@@ -268,6 +269,26 @@ __global__ void __launch_bounds__(256) tf32_pack_kernel(const float* __restrict_
 
 // output channels per CTA: 64 wherever it divides (4 row blocks x 2 accumulator sets x 64 = all 512 TMEM columns, so
 // every weight stage is shared by 512 frames), else the whole of a narrow layer (mel_linear / PostNet's 80)
+// strided gather of a [Cout, Cin] matrix per (b, h) into the packed k = 1 stage layout; co fastest across threads
+__global__ void __launch_bounds__(256) tf32_pack_strided_kernel(const float* __restrict__ src, size_t bs, size_t hs, size_t ld_co,
+                                                                size_t ld_ci, int heads, int Cout, int Cin, int co_valid, int ci_valid,
+                                                                int n_t, float* __restrict__ packed) {
+    const int z = blockIdx.y;
+    const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (e >= (long long)Cout * Cin) return;
+    int co, ci;
+    if (ld_co <= ld_ci) { co = (int)(e % Cout); ci = (int)(e / Cout); }      // the contiguous source axis runs across threads
+    else { ci = (int)(e % Cin); co = (int)(e / Cin); }
+    float v = 0.f;
+    if (co < co_valid && ci < ci_valid) v = src[(size_t)(z / heads) * bs + (size_t)(z % heads) * hs + (size_t)co * ld_co + (size_t)ci * ld_ci];
+    const float hi = tf32_round(v), lo = tf32_round(v - hi);
+    const int tile = co / n_t, r = co % n_t, c = ci / T32_KC, kk = ci % T32_KC, chunks = Cin / T32_KC;
+    const size_t stage = (size_t)tile * chunks + c;
+    const size_t idx = (size_t)z * 2 * Cout * Cin + stage * (size_t)(16 * n_t) + (size_t)(kk >> 2) * (n_t * 8) + (size_t)r * 4 + (kk & 3);
+    packed[idx] = hi;
+    packed[idx + 4 * (size_t)n_t] = lo;
+}
+
 int tile_width(int Cout) {
     if (Cout % 64 == 0) return 64;
     if (Cout <= 128 && Cout % 16 == 0) return Cout;
@@ -281,7 +302,7 @@ int launch(const T32K& kp, size_t smem, cudaStream_t st) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(tf32_conv_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
         attr = true;
     }
-    dim3 grid((unsigned)vo2w_ceil_div(kp.c.L, 128 * NB), (unsigned)kp.n_tiles, (unsigned)kp.c.B);
+    dim3 grid((unsigned)vo2w_ceil_div(kp.c.L, 128 * NB), (unsigned)kp.n_tiles, (unsigned)(kp.c.B * kp.c.heads));
     tf32_conv_kernel<NB><<<grid, T32_THREADS, smem, st>>>(kp);
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
@@ -303,6 +324,17 @@ int tf32_conv_pack(const float* w, int Cout, int Cin, int k, float* packed, cuda
     return VO2W_OK;
 }
 
+int tf32_pack_strided(const float* src, size_t bs, size_t hs, size_t ld_co, size_t ld_ci, int B, int heads, int Cout, int Cin,
+                      int co_valid, int ci_valid, float* packed, cudaStream_t st) {
+    VO2W_REQUIRE(tf32_conv_supported(Cout, Cin, 1) && B > 0 && heads > 0 && (long long)B * heads <= 65535,
+                 "tf32 pack: shape Cout %d Cin %d unsupported", Cout, Cin);
+    dim3 grid((unsigned)vo2w_ceil_div((long long)Cout * Cin, 256), (unsigned)(B * heads));
+    tf32_pack_strided_kernel<<<grid, 256, 0, st>>>(src, bs, hs, ld_co, ld_ci, heads, Cout, Cin, co_valid, ci_valid, tile_width(Cout),
+                                                   packed);
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}
+
 int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     VO2W_REQUIRE(tf32_conv_supported(c.Cout, c.Cin, c.k), "tf32 conv: shape Cout %d Cin %d k %d unsupported", c.Cout, c.Cin, c.k);
     VO2W_REQUIRE(c.B > 0 && c.B <= 65535 && c.L > 0, "tf32 conv: bad batch (B=%d L=%d)", c.B, c.L);
@@ -310,6 +342,11 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
                  "tf32 conv: pointers must be 16-byte aligned");
     T32K kp;
     kp.c = c;
+    if (kp.c.ldx == 0) kp.c.ldx = c.Cin;
+    if (kp.c.ldo == 0) kp.c.ldo = c.Cout;
+    if (kp.c.heads < 1) kp.c.heads = 1;
+    VO2W_REQUIRE(kp.c.ldx % 4 == 0 && kp.c.ldo % 4 == 0 && kp.c.x_hs % 4 == 0 && kp.c.o_hs % 4 == 0 && kp.c.w_zs % 4 == 0 &&
+                 (long long)c.B * kp.c.heads <= 65535, "tf32 conv: strides must be multiples of 4 floats, B * heads <= 65535");
     kp.n_t = tile_width(c.Cout);
     kp.n_tiles = c.Cout / kp.n_t;
     kp.chunks = c.Cin / T32_KC;

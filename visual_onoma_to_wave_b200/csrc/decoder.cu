@@ -169,7 +169,69 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const float* __rest
     }
 }
 
+// in place: S[r, 0..Lp) -> softmax(S[r, :] * scale) over the valid keys (j < L and not padding), zeros elsewhere
+// (attn / temperature, masked_fill(mask, -inf), Softmax(dim=2): Modules.py:15-22).  rows r = (b, l, h); one warp per row.
+__global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S, const uint8_t* __restrict__ mask, long long rows,
+                                                           int L, int Lp, int rows_per_b, float scale) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    float* row = S + (size_t)r * Lp;
+    const uint8_t* mb = mask ? mask + (size_t)(r / rows_per_b) * L : nullptr;
+    constexpr int MAXP = 32;                          // Lp <= 1024 per pass in registers
+    float v[MAXP];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < MAXP; ++i) {
+        const int j = lane + 32 * i;
+        v[i] = -INFINITY;
+        if (j < L && !(mb && mb[j])) v[i] = row[j] * scale;
+        mx = fmaxf(mx, v[i]);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXP; ++i) {
+        v[i] = expf(v[i] - mx);                       // -inf - mx -> 0; an all-masked row gives NaN like the reference
+        if (lane + 32 * i < Lp) sum += v[i];
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.f / sum;
+#pragma unroll
+    for (int i = 0; i < MAXP; ++i) {
+        const int j = lane + 32 * i;
+        if (j < Lp) row[j] = v[i] * inv;
+    }
+}
+
 }  // namespace
+
+// Attention as two batched GEMMs on the tensor pipe (conv_tf32.cu, fp32-level accuracy) around a row softmax:
+//   S[b,l,h,:] = q_h[b,l,:] . k_h[b,:,:]^T      (k = 1 "convolution" whose weights are head h's keys of utterance b)
+//   P = softmax(S / sqrt(d_k)) over the unmasked keys
+//   out[b,l,h*128:] = P[b,l,h,:] . v_h[b,:,:]   (weights = the values, transposed while packing)
+// S / P live in the workspace as [B, L, H, Lp], Lp = L rounded up to 64 (zero probability on the padding columns).
+int rows_attention_gemm(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, float* S, float* pk,
+                        float* pv, cudaStream_t st) {
+    VO2W_REQUIRE(D == n_head * AD, "attention: head size must be %d (d_model %d, heads %d)", AD, D, n_head);
+    const int Lp = (L + 63) / 64 * 64;
+    VO2W_REQUIRE(Lp <= 1024, "attention: %d frames: the row softmax holds at most 1024 keys", L);
+    const size_t row3 = (size_t)3 * D;
+    int rc = tf32_pack_strided(qkv + D, (size_t)L * row3, AD, row3, 1, B, n_head, Lp, AD, L, AD, pk, st);
+    if (rc != VO2W_OK) return rc;
+    Tf32Conv qk{qkv, pk, nullptr, nullptr, S, B, L, AD, Lp, 1, 0};
+    qk.ldx = (int)row3; qk.x_hs = AD; qk.ldo = n_head * Lp; qk.o_hs = Lp; qk.heads = n_head; qk.w_zs = (size_t)2 * Lp * AD;
+    if ((rc = tf32_conv1d(qk, st)) != VO2W_OK) return rc;
+    const long long rows = (long long)B * L * n_head;
+    softmax_rows_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
+    VO2W_CUDA_OK(cudaGetLastError());
+    if ((rc = tf32_pack_strided(qkv + 2 * D, (size_t)L * row3, AD, 1, row3, B, n_head, AD, Lp, AD, L, pv, st)) != VO2W_OK) return rc;
+    Tf32Conv pvc{S, pv, nullptr, nullptr, out, B, L, Lp, AD, 1, 0};
+    pvc.ldx = n_head * Lp; pvc.x_hs = Lp; pvc.ldo = D; pvc.o_hs = AD; pvc.heads = n_head; pvc.w_zs = (size_t)2 * Lp * AD;
+    return tf32_conv1d(pvc, st);
+}
 
 int rows_layernorm_mask(const float* x, const float* gamma, const float* beta, const uint8_t* mask, float* y, long long rows, int D,
                         cudaStream_t st) {
@@ -291,7 +353,9 @@ extern "C" int vo2w_decoder_destroy(vo2w_decoder* d) {
 extern "C" size_t vo2w_decoder_workspace_bytes(const vo2w_decoder* d, int B, int L) {
     if (!d || B <= 0 || L <= 0) return 0;
     const size_t bl = (size_t)B * L * 4;
-    return 2 * dec_align(bl * d->d_model) + dec_align(bl * 3 * d->d_model) + dec_align(bl * d->d_inner);
+    const size_t Lp = ((size_t)L + 63) / 64 * 64;
+    return 2 * dec_align(bl * d->d_model) + dec_align(bl * 3 * d->d_model) + dec_align(bl * d->d_inner) +
+           dec_align(bl * d->n_head * Lp) + 2 * dec_align((size_t)B * d->n_head * 2 * Lp * AD * 4);
 }
 
 // x [B,L,D] time-major, pos [L,D] (the sinusoid table's first L rows), mask [B,L] bytes (1 = padding) or null,
@@ -314,6 +378,12 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
     float* qkv = (float*)(ws + 2 * dec_align(bl * D));         // [B,L,3D]
     float* hid = (float*)(ws + 2 * dec_align(bl * D) + dec_align(bl * 3 * D));   // [B,L,d_inner]; first holds the attention output
     const long long rows = (long long)B * L;
+    const size_t Lp = ((size_t)L + 63) / 64 * 64;
+    uint8_t* wa = ws + 2 * dec_align(bl * D) + dec_align(bl * 3 * D) + dec_align(bl * H);
+    float* att_s = (float*)wa;                                  // [B,L,heads,Lp] scores / probabilities
+    float* att_k = (float*)(wa + dec_align(bl * d->n_head * Lp));            // packed keys / values per (b, head)
+    float* att_v = (float*)(wa + dec_align(bl * d->n_head * Lp) + dec_align((size_t)B * d->n_head * 2 * Lp * AD * 4));
+    static const bool simt_attention = getenv("VO2W_ATTN_SIMT") != nullptr;   // measurement switch (tools/)
 
     // enc_seq + position_enc[:, :L]  (Models.py:184-186)
     int rc = rows_add_table(x, pos, cur, B, L, D, st);
@@ -325,7 +395,9 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
         float* dst = i + 1 == d->layers.size() ? out : cur;
         // MultiHeadAttention (SubLayers.py:31-62)
         if ((rc = conv(cur, P + l.pqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 0, st)) != VO2W_OK) return rc;
-        if ((rc = rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)) != VO2W_OK) return rc;
+        rc = (simt_attention || Lp > 1024) ? rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)
+                                           : rows_attention_gemm(qkv, mask, hid, B, L, D, d->n_head, att_s, att_k, att_v, st);
+        if (rc != VO2W_OK) return rc;
         if ((rc = conv(hid, P + l.pfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 0, st)) != VO2W_OK) return rc;
         if ((rc = rows_layernorm_mask(tmp, W + l.ln1g, W + l.ln1b, mask, cur, rows, D, st)) != VO2W_OK) return rc;
         // PositionwiseFeedForward (SubLayers.py:95-104); relu rides the first convolution's epilogue
