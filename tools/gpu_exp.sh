@@ -1,32 +1,12 @@
 #!/bin/bash
-# scratch experiment script (GPU box)
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_parity.py -q -m gpu -k "tf32 or decoder or acoustic or postnet" 2>&1 | grep -E "AssertionError: |passed|failed|^FAILED|Error" | head -30 > gpurun_out/exp_tests.log
-cat gpurun_out/exp_tests.log
-timeout 300 python __graft_entry__.py --smoke 2>&1 | tail -1
-cat > gpurun_out/dec_err.py <<'PY'
-import torch, numpy as np
-import visual_onoma_to_wave_b200 as v
-from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
-from oracle import decoder_oracle as do
-g = np.load("tests/golden/decoder.npz")
-dec = v.Decoder(decoder_config()); dec.load_state_dict(seeded_decoder_state_dict(2468)); dec.eval().cuda()
-y, _ = dec(torch.from_numpy(g["x_full"]).cuda(), torch.from_numpy(g["mask_full"]).cuda())
-print("decoder golden full", float((y.cpu() - torch.from_numpy(g["y_full"])).abs().max()))
-kw = dict(n_layers=6); sdd = seeded_decoder_state_dict(5, **kw)
-dec = v.Decoder(decoder_config(**kw)); dec.load_state_dict(sdd); dec.eval().cuda()
-lens = torch.tensor([490, 257, 64, 65, 1, 128, 300, 33]); L = 490
-x = torch.randn(8, L, 256, generator=torch.Generator().manual_seed(3)); mask = torch.arange(L)[None, :] >= lens[:, None]
-ref, _ = do.decoder_forward(sdd, x, mask); got, _ = dec(x.cuda(), mask.cuda())
-print("decoder 6 layers ragged", float((got.cpu() - ref).abs().max()))
-for B, L in ((64, 479), (16, 479), (64, 172)):
-    x = torch.randn(B, L, 256, device="cuda"); m = torch.zeros(B, L, dtype=torch.bool, device="cuda")
-    for _ in range(2): dec(x, m)
-    torch.cuda.synchronize(); e0 = torch.cuda.Event(True); e1 = torch.cuda.Event(True)
-    e0.record()
-    for _ in range(5): dec(x, m)
-    e1.record(); torch.cuda.synchronize()
-    print(f"decoder B={B} L={L}: {e0.elapsed_time(e1) / 5:.2f} ms")
-PY
-echo "--- gemm attention"; PYTHONPATH=. python gpurun_out/dec_err.py 2>&1 | tail -6
-echo "--- simt attention"; VO2W_ATTN_SIMT=1 PYTHONPATH=. python gpurun_out/dec_err.py 2>&1 | tail -6
+echo "--- n_t 128 for k=1"; PYTHONPATH=. python tools/dec_err.py 2>&1 | tail -5
+echo "--- n_t 128 for all"; VO2W_T32_WIDE=1 PYTHONPATH=. python tools/dec_err.py 2>&1 | tail -5
+python tools/bench_tail.py 2>/dev/null | grep "^{" | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+print({k:round(v['ms'],2) for k,v in d['stages'].items()}, 'chain', round(d['chain_ms'],2))"
+VO2W_T32_WIDE=1 python tools/bench_tail.py 2>/dev/null | grep "^{" | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+print('wide all', {k:round(v['ms'],2) for k,v in d['stages'].items()}, 'chain', round(d['chain_ms'],2))"

@@ -14,11 +14,13 @@
 // which removes the mean of the error for activations-times-weights data: 3.5e-5 -> 1.3e-5 max-abs at n = 320.
 //
 // Geometry: activations are time-major [B,L,C]; one CTA owns NB blocks of 128 consecutive frames of one utterance x
-// one tile of n_t output channels (accumulators: 2 x NB x n_t TMEM columns).  Input channels are walked in chunks of 8
-// (one MMA k-step): per chunk the frames (with the k-1 halo rows, zero outside the utterance) are split and staged
-// K-major in SWIZZLE_NONE core-matrix layout, so tap j of the convolution is the same tile at a row offset of j (16 B
-// per row), exactly as in the bf16 vocoder kernels.  Weights are packed once (tf32_conv_pack) in consumption order
-// and streamed by cp.async.bulk through an mbarrier ring; NB row blocks share every weight stage.
+// one tile of n_t output channels (accumulators: 2 x NB x n_t TMEM columns; n_t = 128, NB = 2 for the wide layers).
+// Input channels are walked in chunks of 8 (one MMA k-step): per chunk the frames (with the k-1 halo rows, zero
+// outside the utterance) are split and staged K-major in SWIZZLE_NONE core-matrix layout, so tap j of the convolution
+// is the same tile at a row offset of j (16 B per row), exactly as in the bf16 vocoder kernels.  Weights are packed
+// once (tf32_conv_pack) in consumption order and streamed by cp.async.bulk through an mbarrier ring; the NB row blocks
+// share every weight stage.  A strided / per-head view of the same kernel (ldx, ldo, heads, w_zs) runs the two batched
+// GEMMs of attention, with the keys / values of each (utterance, head) packed as that GEMM's weights.
 //
 // Warp roles (320 threads): warps 0-7 stage the activation chunks (two groups of four, alternating chunk pairs, so
 // four chunk loads are in flight) and later run the epilogue; warp 8 streams the weights; warp 9 owns TMEM and issues
@@ -267,8 +269,6 @@ __global__ void __launch_bounds__(256) tf32_pack_kernel(const float* __restrict_
     packed[idx + 4 * (size_t)n_t] = lo;
 }
 
-// output channels per CTA: 64 wherever it divides (4 row blocks x 2 accumulator sets x 64 = all 512 TMEM columns, so
-// every weight stage is shared by 512 frames), else the whole of a narrow layer (mel_linear / PostNet's 80)
 // strided gather of a [Cout, Cin] matrix per (b, h) into the packed k = 1 stage layout; co fastest across threads
 __global__ void __launch_bounds__(256) tf32_pack_strided_kernel(const float* __restrict__ src, size_t bs, size_t hs, size_t ld_co,
                                                                 size_t ld_ci, int heads, int Cout, int Cin, int co_valid, int ci_valid,
@@ -289,7 +289,13 @@ __global__ void __launch_bounds__(256) tf32_pack_strided_kernel(const float* __r
     packed[idx + 4 * (size_t)n_t] = lo;
 }
 
-int tile_width(int Cout) {
+// output channels per CTA: 128 wherever it divides (2 row blocks x [main | small] x 128 = all 512 TMEM columns; the
+// stacked [w_hi ; w_lo] MMA is then 256 wide, which shared-memory operand bandwidth favours: measured 8 % faster on
+// the k = 9 / k = 5 layers and 14 % on the k = 1 layers than 64-wide tiles with 4 row blocks), else 64, else the whole
+// of a narrow layer (mel_linear / PostNet's 80)
+int tile_width(int Cout, int k) {
+    (void)k;
+    if (Cout % 128 == 0) return 128;
     if (Cout % 64 == 0) return 64;
     if (Cout <= 128 && Cout % 16 == 0) return Cout;
     return 0;
@@ -311,7 +317,7 @@ int launch(const T32K& kp, size_t smem, cudaStream_t st) {
 }  // namespace
 
 bool tf32_conv_supported(int Cout, int Cin, int k) {
-    return tile_width(Cout) > 0 && Cin > 0 && Cin % T32_KC == 0 && (k & 1) && k >= 1 && k <= 11;
+    return tile_width(Cout, k) > 0 && Cin > 0 && Cin % T32_KC == 0 && (k & 1) && k >= 1 && k <= 11;
 }
 
 size_t tf32_conv_packed_floats(int Cout, int Cin, int k) { return (size_t)2 * Cout * Cin * k; }
@@ -319,7 +325,7 @@ size_t tf32_conv_packed_floats(int Cout, int Cin, int k) { return (size_t)2 * Co
 int tf32_conv_pack(const float* w, int Cout, int Cin, int k, float* packed, cudaStream_t st) {
     VO2W_REQUIRE(tf32_conv_supported(Cout, Cin, k), "tf32 conv: shape Cout %d Cin %d k %d unsupported", Cout, Cin, k);
     const long long n = (long long)Cout * Cin * k;
-    tf32_pack_kernel<<<(unsigned)vo2w_ceil_div(n, 256), 256, 0, st>>>(w, Cout, Cin, k, tile_width(Cout), packed);
+    tf32_pack_kernel<<<(unsigned)vo2w_ceil_div(n, 256), 256, 0, st>>>(w, Cout, Cin, k, tile_width(Cout, k), packed);
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
 }
@@ -329,7 +335,7 @@ int tf32_pack_strided(const float* src, size_t bs, size_t hs, size_t ld_co, size
     VO2W_REQUIRE(tf32_conv_supported(Cout, Cin, 1) && B > 0 && heads > 0 && (long long)B * heads <= 65535,
                  "tf32 pack: shape Cout %d Cin %d unsupported", Cout, Cin);
     dim3 grid((unsigned)vo2w_ceil_div((long long)Cout * Cin, 256), (unsigned)(B * heads));
-    tf32_pack_strided_kernel<<<grid, 256, 0, st>>>(src, bs, hs, ld_co, ld_ci, heads, Cout, Cin, co_valid, ci_valid, tile_width(Cout),
+    tf32_pack_strided_kernel<<<grid, 256, 0, st>>>(src, bs, hs, ld_co, ld_ci, heads, Cout, Cin, co_valid, ci_valid, tile_width(Cout, 1),
                                                    packed);
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
@@ -347,7 +353,7 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     if (kp.c.heads < 1) kp.c.heads = 1;
     VO2W_REQUIRE(kp.c.ldx % 4 == 0 && kp.c.ldo % 4 == 0 && kp.c.x_hs % 4 == 0 && kp.c.o_hs % 4 == 0 && kp.c.w_zs % 4 == 0 &&
                  (long long)c.B * kp.c.heads <= 65535, "tf32 conv: strides must be multiples of 4 floats, B * heads <= 65535");
-    kp.n_t = tile_width(c.Cout);
+    kp.n_t = tile_width(c.Cout, c.k);
     kp.n_tiles = c.Cout / kp.n_t;
     kp.chunks = c.Cin / T32_KC;
     int NB = c.L > 256 ? 4 : (c.L > 128 ? 2 : 1);
@@ -355,7 +361,7 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     // k = 1 layers are bound by the latency of the activation loads, not by the weight stream: half-size CTAs (two
     // per SM by registers, shared memory and TMEM columns) keep twice the loads in flight and hide each other's
     // prologue / epilogue
-    if (c.k == 1) while (NB > 1 && 2 * NB * kp.n_t > 256) NB /= 2;
+    if (c.k == 1 && kp.n_t <= 64) while (NB > 1 && 2 * NB * kp.n_t > 256) NB /= 2;
     kp.R = NB * 128 + c.k - 1;
     kp.R8 = (kp.R + 7) / 8 * 8;
     kp.a_stage_bytes = (uint32_t)(4 * kp.R8 * 16);

@@ -383,7 +383,6 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
     float* att_s = (float*)wa;                                  // [B,L,heads,Lp] scores / probabilities
     float* att_k = (float*)(wa + dec_align(bl * d->n_head * Lp));            // packed keys / values per (b, head)
     float* att_v = (float*)(wa + dec_align(bl * d->n_head * Lp) + dec_align((size_t)B * d->n_head * 2 * Lp * AD * 4));
-    static const bool simt_attention = getenv("VO2W_ATTN_SIMT") != nullptr;   // measurement switch (tools/)
 
     // enc_seq + position_enc[:, :L]  (Models.py:184-186)
     int rc = rows_add_table(x, pos, cur, B, L, D, st);
@@ -395,7 +394,7 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
         float* dst = i + 1 == d->layers.size() ? out : cur;
         // MultiHeadAttention (SubLayers.py:31-62)
         if ((rc = conv(cur, P + l.pqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 0, st)) != VO2W_OK) return rc;
-        rc = (simt_attention || Lp > 1024) ? rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)
+        rc = Lp > 1024 ? rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)       // longer than the row softmax holds
                                            : rows_attention_gemm(qkv, mask, hid, B, L, D, d->n_head, att_s, att_k, att_v, st);
         if (rc != VO2W_OK) return rc;
         if ((rc = conv(hid, P + l.pfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 0, st)) != VO2W_OK) return rc;
