@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int l0 = blockIdx.x * 128 * NB, tile = blockIdx.y;
     const int b = (int)blockIdx.z / p.c.heads, zh = (int)blockIdx.z % p.c.heads;          // heads >= 1 (host)
-    const int k = p.c.k, pad = (k - 1) / 2, L = p.c.L, ldx = p.c.ldx, n_t = p.n_t, R8 = p.R8;
+    const int k = p.c.k, dil = p.c.dil, pad = dil * (k - 1) / 2, L = p.c.L, ldx = p.c.ldx, n_t = p.n_t, R8 = p.R8;
 
     const uint32_t a_ring = smem_u32(smem);
     const uint32_t w_ring = a_ring + T32_AS * p.a_stage_bytes;
@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         // contiguous bytes per frame: lane = (16-byte segment, row) so that one warp load touches 8 rows x 64 B (8 cache
         // lines, not 32) and one quarter-warp store phase writes 128 contiguous bytes of one k-column.
         const int g = warp >> 2, wq = warp & 3, seg = lane >> 3, r_in = wq * 8 + (lane & 7);
-        constexpr int NRI = NB * 4 + 1;                  // row iterations: (NB*128 + halo, rounded to 8) / 32 rows per pass
+        constexpr int NRI = NB * 4 + 2;                  // row iterations: (NB*128 + halo <= 50, rounded to 8) / 32 rows per pass
+        const float slope = p.c.in_slope;
         const float* xb = p.c.x + (size_t)b * L * ldx + (size_t)zh * p.c.x_hs;
         for (int c0 = 2 * g; c0 < p.chunks; c0 += 4) {
             const bool pair = c0 + 1 < p.chunks;
@@ -119,9 +120,10 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
 #pragma unroll
             for (int i = 0; i < NRI; ++i) {
                 const int r = i * 32 + r_in, l = l0 - pad + r;
-                if (mine && r < p.R && l >= 0 && l < L)
+                if (mine && r < p.R && l >= 0 && l < L) {
                     v[i] = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * ldx + c0 * T32_KC) + seg);
-                else
+                    v[i].x = lrelu(v[i].x, slope); v[i].y = lrelu(v[i].y, slope); v[i].z = lrelu(v[i].z, slope); v[i].w = lrelu(v[i].w, slope);
+                } else
                     v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             const int s0 = c0 % T32_AS, s1 = (c0 + 1) % T32_AS, use = c0 / T32_AS;      // c0 is even: same `use` for both
@@ -184,6 +186,13 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
 #pragma unroll
                     for (int i = 0; i < 4; ++i) { const float4 t = __ldg(rp + i); y[4 * i] += t.x; y[4 * i + 1] += t.y; y[4 * i + 2] += t.z; y[4 * i + 3] += t.w; }
                 }
+                if (p.c.acc) {
+                    const float4* ap = reinterpret_cast<const float4*>(p.c.acc + row + cc * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { const float4 t = ap[i]; y[4 * i] += t.x; y[4 * i + 1] += t.y; y[4 * i + 2] += t.z; y[4 * i + 3] += t.w; }
+                }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) y[i] *= p.c.out_scale;
                 if (p.c.act == 1) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) y[i] = fmaxf(y[i], 0.f);
@@ -235,7 +244,7 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
                     const uint32_t first = (c | j) ? 1u : 0u;
 #pragma unroll
                     for (int blk = 0; blk < NB; ++blk) {
-                        const uint64_t a_hi = a_stage + (uint64_t)(uint32_t)(blk * 128 + j), a_lo = a_hi + a_lo_u;
+                        const uint64_t a_hi = a_stage + (uint64_t)(uint32_t)(blk * 128 + j * dil), a_lo = a_hi + a_lo_u;
                         const uint32_t d_main = tmem_base + (uint32_t)(blk * 2 * n_t);
                         umma_tf32(d_main, a_hi, b_desc, idesc2, first);                  // [main | small] (+)= a_hi . [w_hi ; w_lo]
                         umma_tf32(d_main + (uint32_t)n_t, a_lo, b_desc, idesc1, 1u);       // small += a_lo . w_hi
@@ -351,6 +360,10 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     if (kp.c.ldx == 0) kp.c.ldx = c.Cin;
     if (kp.c.ldo == 0) kp.c.ldo = c.Cout;
     if (kp.c.heads < 1) kp.c.heads = 1;
+    if (kp.c.dil < 1) kp.c.dil = 1;
+    if (kp.c.in_slope == 0.f) kp.c.in_slope = 1.f;
+    if (kp.c.out_scale == 0.f) kp.c.out_scale = 1.f;
+    VO2W_REQUIRE((c.k - 1) * kp.c.dil <= 50 && (((uintptr_t)c.acc) & 15) == 0, "tf32 conv: halo (k-1)*dil = %d rows > 50", (c.k - 1) * kp.c.dil);
     VO2W_REQUIRE(kp.c.ldx % 4 == 0 && kp.c.ldo % 4 == 0 && kp.c.x_hs % 4 == 0 && kp.c.o_hs % 4 == 0 && kp.c.w_zs % 4 == 0 &&
                  (long long)c.B * kp.c.heads <= 65535, "tf32 conv: strides must be multiples of 4 floats, B * heads <= 65535");
     kp.n_t = tile_width(c.Cout, c.k);
@@ -362,7 +375,7 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     // per SM by registers, shared memory and TMEM columns) keep twice the loads in flight and hide each other's
     // prologue / epilogue
     if (c.k == 1 && kp.n_t <= 64) while (NB > 1 && 2 * NB * kp.n_t > 256) NB /= 2;
-    kp.R = NB * 128 + c.k - 1;
+    kp.R = NB * 128 + (c.k - 1) * kp.c.dil;
     kp.R8 = (kp.R + 7) / 8 * 8;
     kp.a_stage_bytes = (uint32_t)(4 * kp.R8 * 16);
     kp.w_stage_bytes = (uint32_t)(64 * kp.n_t);

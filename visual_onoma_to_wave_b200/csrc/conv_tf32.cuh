@@ -18,6 +18,11 @@ struct Tf32Conv {
     int heads = 0;       // > 1: grid z = B * heads; head h reads x columns h * x_hs.., writes out columns h * o_hs..
     int x_hs = 0, o_hs = 0;
     size_t w_zs = 0;     // packed-weight stride per (b, h) in floats (0: one weight set for every z)
+    // optional vocoder fusions (fp32 mode of the Generator): zero-initialised fields mean "off"
+    int dil = 0;                 // dilation (0: 1); padding dil * (k - 1) / 2
+    float in_slope = 0.f;        // leaky-relu slope applied to x while staging (0: identity)
+    const float* acc = nullptr;  // second addend [B,L,Cout] (MRF sum); may alias out
+    float out_scale = 0.f;       // result scaled before the activation (0: 1), e.g. 1 / num_kernels
 };
 
 bool tf32_conv_supported(int Cout, int Cin, int k);

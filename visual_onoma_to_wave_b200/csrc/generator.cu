@@ -8,11 +8,14 @@
 //                   iteration of all ResBlocks of a stage plus the MRF average is one launch too;
 //                   activations travel through HBM as bf16;
 //   VO2W_PREC_FP32  CUDA-core fp32 kernels (conv_simt.cu) on plain NCL tensors.
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
 
 #include "conv_simt.cuh"
+#include "conv_tf32.cuh"
+#include "rows.cuh"
 #include "pack.cuh"
 #include "pair_umma.cuh"
 
@@ -53,6 +56,12 @@ struct vo2w_generator {
     std::vector<LayerW> lw;        // conv_pre, ups[i], resblocks[n].convs1[m], .convs2[m], conv_post (state-dict order)
     size_t n_floats = 0;
     float* w_dev = nullptr;        // fp32 blob on the device (fp32 mode + biases)
+    // fp32 mode: every layer but conv_post packed for the tensor-pipe kernel (conv_tf32.cu); a ConvTranspose1d becomes a
+    // k = 3 convolution onto stride * Cout phase-major channels (see ups_as_conv_kernel)
+    float* p32 = nullptr;
+    std::vector<size_t> p32_off;   // per layer of `lw`
+    float* ups_bias = nullptr;     // bias replicated per phase, ups_bias_off[i]
+    size_t ups_bias_off[4] = {};
     // bf16 mode
     PackedLayer conv_pre, conv_post, ups[4];
     PackedPair pairs[12][3];       // resblocks[n] iteration m: convs1[m] + convs2[m]
@@ -160,6 +169,77 @@ int build_layer_table(vo2w_generator* g, size_t n_floats) {
 
 }  // namespace
 
+namespace {
+
+// ConvTranspose1d(stride s, kernel ks = 2 s, padding (ks - s) / 2) as a Conv1d with 3 taps onto s * Cout channels:
+//   out[l * s + ph] = sum_t x[l + floor((ph + p) / s) - t] . w[:, :, (ph + p) % s + t * s],  t = 0 .. ks / s - 1,
+// so with channel ph * Cout + co the time-major result [L, s * Cout] IS the upsampled [L * s, Cout] tensor.
+// w [Cin, Cout, ks] (ConvTranspose1d layout) -> weff [s * Cout, Cin, 3] (Conv1d layout), zero where a tap is unused.
+__global__ void __launch_bounds__(256) ups_as_conv_kernel(const float* __restrict__ w, int Cin, int Cout, int ks, int s,
+                                                          float* __restrict__ weff) {
+    const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (e >= (long long)s * Cout * Cin * 3) return;
+    const int tau = (int)(e % 3), ci = (int)((e / 3) % Cin), ce = (int)(e / (3LL * Cin));
+    const int ph = ce / Cout, co = ce % Cout, p = (ks - s) / 2;
+    const int t = (ph + p) / s - (tau - 1), j = (ph + p) % s + t * s;
+    weff[e] = (t >= 0 && j < ks) ? w[((size_t)ci * Cout + co) * ks + j] : 0.f;
+}
+
+int pack_fp32_mode(vo2w_generator* g) {
+    const vo2w_gen_config& cfg = g->cfg;
+    size_t total = 0, bias_total = 0, scratch = 0;
+    g->p32_off.assign(g->lw.size(), 0);
+    for (size_t i = 0; i < g->lw.size(); ++i) {
+        const LayerW& l = g->lw[i];
+        const bool up = (int)i >= idx_ups(0) && (int)i < idx_ups(g->n_stage);
+        g->p32_off[i] = total;
+        if ((int)i == idx_conv_post(g)) continue;                 // Cout = 1: stays on the CUDA-core kernel
+        if (up) {
+            const int s = cfg.upsample_rates[i - idx_ups(0)];
+            VO2W_REQUIRE(l.k == 2 * s && tf32_conv_supported(s * l.d1, l.d0, 3), "fp32 mode: upsampler %zu (k %d, stride %d, %d -> %d) unsupported",
+                         i - idx_ups(0), l.k, s, l.d0, l.d1);
+            total += tf32_conv_packed_floats(s * l.d1, l.d0, 3);
+            scratch = std::max(scratch, (size_t)s * l.d1 * l.d0 * 3);
+            g->ups_bias_off[i - idx_ups(0)] = bias_total;
+            bias_total += (size_t)s * l.d1;
+        } else {
+            VO2W_REQUIRE(tf32_conv_supported(l.d0, l.d1, l.k), "fp32 mode: layer %zu (%d -> %d, k %d) unsupported", i, l.d1, l.d0, l.k);
+            total += tf32_conv_packed_floats(l.d0, l.d1, l.k);
+        }
+    }
+    float* tmp = nullptr;
+    if (cudaMalloc(&g->p32, total * 4) != cudaSuccess || cudaMalloc(&g->ups_bias, bias_total * 4) != cudaSuccess ||
+        cudaMalloc(&tmp, scratch * 4) != cudaSuccess) {
+        if (tmp) cudaFree(tmp);
+        vo2w_set_error("generator_create: allocating packed fp32-mode weights failed");
+        return VO2W_E_CUDA;
+    }
+    int rc = VO2W_OK;
+    for (size_t i = 0; i < g->lw.size() && rc == VO2W_OK; ++i) {
+        const LayerW& l = g->lw[i];
+        const bool up = (int)i >= idx_ups(0) && (int)i < idx_ups(g->n_stage);
+        if ((int)i == idx_conv_post(g)) continue;
+        if (up) {
+            const int st = (int)i - idx_ups(0), s = cfg.upsample_rates[st];
+            const long long n = (long long)s * l.d1 * l.d0 * 3;
+            ups_as_conv_kernel<<<(unsigned)vo2w_ceil_div(n, 256), 256>>>(g->w_dev + l.w_off, l.d0, l.d1, l.k, s, tmp);
+            rc = tf32_conv_pack(tmp, s * l.d1, l.d0, 3, g->p32 + g->p32_off[i], 0);
+            for (int ph = 0; ph < s && rc == VO2W_OK; ++ph)
+                if (cudaMemcpy(g->ups_bias + g->ups_bias_off[st] + (size_t)ph * l.d1, g->w_dev + l.b_off, (size_t)l.d1 * 4,
+                               cudaMemcpyDeviceToDevice) != cudaSuccess) rc = VO2W_E_CUDA;
+            if (cudaDeviceSynchronize() != cudaSuccess) rc = VO2W_E_CUDA;       // tmp is reused by the next upsampler
+        } else {
+            rc = tf32_conv_pack(g->w_dev + l.w_off, l.d0, l.d1, l.k, g->p32 + g->p32_off[i], 0);
+        }
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess) rc = VO2W_E_CUDA;
+    cudaFree(tmp);
+    if (rc != VO2W_OK) vo2w_set_error("generator_create: packing fp32-mode weights failed");
+    return rc;
+}
+
+}  // namespace
+
 extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* weights_host, size_t n_floats,
                                      int precision, vo2w_generator** out) {
     VO2W_REQUIRE(cfg && weights_host && out, "generator_create: null argument");
@@ -220,6 +300,7 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
             VO2W_TRY(make_group(g->mrf_group[i], last, g->nk));
         }
     }
+    if (precision == VO2W_PREC_FP32) VO2W_TRY(pack_fp32_mode(g));
 #undef VO2W_TRY
     *out = g;
     return VO2W_OK;
@@ -228,6 +309,8 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
 extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
     if (!g) return VO2W_OK;
     if (g->w_dev) cudaFree(g->w_dev);
+    if (g->p32) cudaFree(g->p32);
+    if (g->ups_bias) cudaFree(g->ups_bias);
     for (cudaEvent_t e : g->ev) cudaEventDestroy(e);
     free_layer(g->conv_pre);
     free_layer(g->conv_post);
@@ -352,36 +435,37 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
     return VO2W_OK;
 }
 
-// Same schedule on the fp32 CUDA-core kernels (NCL tensors).
+// fp32 mode: the same schedule on the tensor pipe with fp32-level accuracy (conv_tf32.cu: kind::tf32, hi/lo operand
+// split), time-major [B,L,C] tensors.  leaky-relu rides the activation staging, bias / residual / MRF sum / average
+// the epilogue; a ConvTranspose1d is a 3-tap convolution onto stride x Cout phase-major channels, whose time-major
+// result is the upsampled tensor as it stands.  conv_post (one output channel) runs on the CUDA-core kernel.
 int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
     const int B = p.B, T = p.T;
     auto f32 = [&](size_t off) { return (float*)(ws + off); };
-    auto W = [&](int idx) { return g->w_dev + g->lw[idx].w_off; };
     auto Bi = [&](int idx) { return g->w_dev + g->lw[idx].b_off; };
-    SimtConv c;
-    memset(&c, 0, sizeof(c));
-    c.B = B;
-    c.stride = 1;
-    c.div = 1.f;
+    auto P = [&](int idx) { return g->p32 + g->p32_off[idx]; };
+    auto conv = [&](const float* x, int idx, const float* bias, const float* res, const float* acc, float* out, int L, int Cin,
+                    int Cout, int k, int dil, float in_slope, float out_scale) {
+        Tf32Conv c{x, P(idx), bias, res, out, B, L, Cin, Cout, k, 0};
+        c.dil = dil; c.in_slope = in_slope; c.acc = acc; c.out_scale = out_scale;
+        return tf32_conv1d(c, st);
+    };
     {
+        // mel [B,80,T] -> [B,T,80]; conv_pre
         const LayerW& l = g->lw[idx_conv_pre()];
-        SimtConv q = c;
-        q.x = mel; q.w = W(0); q.bias = Bi(0); q.out = f32(p.c0_f32);
-        q.Cin = l.d1; q.Cout = l.d0; q.L = T; q.k = l.k; q.dil = 1; q.pad = 3; q.in_slope = 1.f;
-        VO2W_RUN(simt_conv1d(q, st));
+        float* mel_t = f32(p.st[0].tt);
+        VO2W_RUNK(0, rows_transpose_add(mel, nullptr, mel_t, B, l.d1, T, st));
+        VO2W_RUN(conv(mel_t, idx_conv_pre(), Bi(0), nullptr, nullptr, f32(p.c0_f32), T, l.d1, l.d0, l.k, 1, 1.f, 1.f));
     }
     const float* x_in = f32(p.c0_f32);
     long long L_in = T;
     for (int i = 0; i < g->n_stage; ++i) {
         const StageBufs& s = p.st[i];
         {
-            const int idx = idx_ups(i);
+            const int idx = idx_ups(i), up = g->cfg.upsample_rates[i];
             const LayerW& l = g->lw[idx];
-            SimtConv q = c;
-            q.x = x_in; q.w = W(idx); q.bias = Bi(idx); q.out = f32(s.x_f32);
-            q.Cin = l.d0; q.Cout = l.d1; q.L = (int)L_in; q.k = l.k; q.stride = g->cfg.upsample_rates[i];
-            q.pad = (l.k - q.stride) / 2; q.in_slope = 0.1f;
-            VO2W_RUN(simt_convt1d(q, st));
+            VO2W_RUN(conv(x_in, idx, g->ups_bias + g->ups_bias_off[i], nullptr, nullptr, f32(s.x_f32), (int)L_in, l.d0, up * l.d1, 3, 1,
+                          0.1f, 1.f));
         }
         for (int j = 0; j < g->nk; ++j) {
             const int n = i * g->nk + j;
@@ -389,32 +473,31 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             for (int m = 0; m < 3; ++m) {
                 const int d = g->cfg.resblock_dilation_sizes[j][m];
                 const float* xin = m == 0 ? f32(s.x_f32) : f32(s.rr);
-                SimtConv q = c;
                 int idx = idx_rb(g, n, 0, m);
-                q.x = xin; q.w = W(idx); q.bias = Bi(idx); q.out = f32(s.tt);
-                q.Cin = q.Cout = s.C; q.L = (int)s.L; q.k = k; q.dil = d; q.pad = d * (k - 1) / 2; q.in_slope = 0.1f;
-                VO2W_RUN(simt_conv1d(q, st));
+                VO2W_RUN(conv(xin, idx, Bi(idx), nullptr, nullptr, f32(s.tt), (int)s.L, s.C, s.C, k, d, 0.1f, 1.f));
                 idx = idx_rb(g, n, 1, m);
-                q.x = f32(s.tt); q.w = W(idx); q.bias = Bi(idx); q.dil = 1; q.pad = (k - 1) / 2;
-                q.res = xin;
                 if (m < 2) {
-                    q.out = f32(s.rr);
+                    VO2W_RUN(conv(f32(s.tt), idx, Bi(idx), xin, nullptr, f32(s.rr), (int)s.L, s.C, s.C, k, 1, 0.1f, 1.f));
                 } else {            // xs (+)= resblock_j(x); after the last one x = xs / num_kernels
-                    q.out = f32(s.xs);
-                    q.accum = j == 0 ? 0 : 1;
-                    if (j == g->nk - 1 && g->nk > 1) { q.accum = 2; q.div = (float)g->nk; }
+                    const bool last = j == g->nk - 1 && g->nk > 1;
+                    VO2W_RUN(conv(f32(s.tt), idx, Bi(idx), xin, j == 0 ? nullptr : f32(s.xs), f32(s.xs), (int)s.L, s.C, s.C, k, 1, 0.1f,
+                                  last ? 1.0f / (float)g->nk : 1.f));
                 }
-                VO2W_RUN(simt_conv1d(q, st));
             }
         }
         x_in = f32(s.xs);
         L_in = s.L;
     }
     {
+        // conv_post: [B,L,C] -> [B,C,L], then the CUDA-core kernel (Cout = 1) with leaky-relu 0.01 in, tanh out
+        const StageBufs& s = p.st[g->n_stage - 1];
         const int idx = idx_conv_post(g);
         const LayerW& l = g->lw[idx];
-        SimtConv q = c;
-        q.x = x_in; q.w = W(idx); q.bias = Bi(idx); q.out = wav;
+        VO2W_RUNK(0, rows_transpose_add(x_in, nullptr, f32(s.tt), B, (int)L_in, l.d1, st));
+        SimtConv q;
+        memset(&q, 0, sizeof(q));
+        q.B = B; q.stride = 1; q.div = 1.f;
+        q.x = f32(s.tt); q.w = g->w_dev + l.w_off; q.bias = Bi(idx); q.out = wav;
         q.Cin = l.d1; q.Cout = 1; q.L = (int)L_in; q.k = l.k; q.dil = 1; q.pad = 3; q.in_slope = 0.01f; q.tanh_out = 1;
         VO2W_RUN(simt_conv1d(q, st));
     }
@@ -537,8 +620,13 @@ extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap
         if (rc == VO2W_OK && cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = VO2W_E_CUDA;
         cudaFree(tmp);
         if (rc != VO2W_OK) return rc;
-    } else {
-        VO2W_CUDA_OK(cudaMemcpy(out_host, ws + off, n * 4, cudaMemcpyDeviceToHost));
+    } else {                       // fp32 mode keeps [B,L,C]: hand out the reference's [B,C,L]
+        float* tmp = nullptr;
+        VO2W_CUDA_OK(cudaMalloc(&tmp, n * 4));
+        int rc = rows_transpose_add((const float*)(ws + off), nullptr, tmp, p.B, (int)L, C, 0);
+        if (rc == VO2W_OK && cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = VO2W_E_CUDA;
+        cudaFree(tmp);
+        if (rc != VO2W_OK) return rc;
     }
     return (long long)n;
 }
