@@ -287,6 +287,32 @@ def run_ours(args):
             extra["length_regulator"] = lr_bandwidth(dev, peaks)
         except Exception as e:  # reported, not fatal for the vocoder metric
             extra["length_regulator"] = {"error": str(e)}
+        if world == 1 and args.precision == "bf16":
+            try:   # the exact mode (max-abs-err <= 1e-4 gate): same Generator on the tf32 hi/lo-split tensor-pipe kernel
+                g32 = v.Generator(v.AttrDict(V1_CONFIG), precision="fp32")
+                g32.eval()
+                with contextlib.redirect_stdout(sys.stderr):
+                    g32.remove_weight_norm()
+                g32.load_state_dict(seeded_state_dict(1234))
+                g32.to(dev)
+                m32 = mel_dev[:64]
+                for _ in range(2):
+                    g32(m32)
+                torch.cuda.synchronize(dev)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    g32(m32)
+                e1.record()
+                torch.cuda.synchronize(dev)
+                ms32 = e0.elapsed_time(e1) / 3
+                nb = m32.shape[0]
+                extra["fp32_mode"] = {"utterances": nb, "ms": ms32, "audio_s_per_s": nb * T_FRAMES * 256 / 22050 / ms32 * 1e3,
+                                      "tflops_fp32_equivalent": FLOP_PER_FRAME * nb * T_FRAMES / ms32 / 1e9,
+                                      "kernel": "tf32_conv_kernel: tcgen05 kind::tf32, 3 products per fp32 product"}
+                del g32
+            except Exception as e:
+                extra["fp32_mode"] = {"error": str(e)}
         if world == 1:
             try:   # the acoustic tail in front of the vocoder, device timing per stage
                 sys.path.insert(0, os.path.join(ROOT, "tools"))
