@@ -40,7 +40,7 @@ extern "C" {
 #define VO2W_DUR_F64 3
 
 /* precision modes of the Generator */
-#define VO2W_PREC_FP32 0   /* CUDA-core fp32 kernels: max-abs-err <= 1e-4 gate            */
+#define VO2W_PREC_FP32 0   /* tcgen05 kind::tf32, hi/lo operand split: max-abs-err <= 1e-4 */
 #define VO2W_PREC_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate: SNR >= 40 dB */
 
 /* HiFi-GAN hyper-parameters read by Generator.__init__ (scripts/hifigan/models.py:116-143,

@@ -7,7 +7,7 @@
 //                   upsamplers / conv_post are single-conv launches (conv_umma.cu); the last
 //                   iteration of all ResBlocks of a stage plus the MRF average is one launch too;
 //                   activations travel through HBM as bf16;
-//   VO2W_PREC_FP32  CUDA-core fp32 kernels (conv_simt.cu) on plain NCL tensors.
+//   VO2W_PREC_FP32  tcgen05 kind::tf32 kernels with a hi/lo operand split (conv_tf32.cu) on time-major fp32 tensors.
 #include <algorithm>
 #include <map>
 #include <string>
@@ -35,7 +35,7 @@ struct StageBufs {         // per upsampling stage, offsets in bytes into the wo
     size_t xa = 0;                 // ups output
     size_t ra[3][2] = {};          // ResBlock j after iteration 0 / 1
     size_t mrf = 0;                // leaky-relu(xs / num_kernels) = operand of the next layer
-    // fp32 mode (NCL)
+    // fp32 mode (time-major [B,L,C])
     size_t x_f32 = 0, rr = 0, tt = 0, xs = 0;
 };
 

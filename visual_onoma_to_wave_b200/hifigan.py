@@ -98,7 +98,7 @@ class Generator(nn.Module):
     """HiFi-GAN generator, mel [B,80,T] -> wav [B,1,T*prod(upsample_rates)] (models.py:112-174).
 
     precision: "bf16" (tcgen05 tensor-core kernels, SNR >= 40 dB vs the fp32 reference) or
-    "fp32" (CUDA-core kernels, max-abs-err <= 1e-4).  Default from $VO2W_PRECISION, else "bf16".
+    "fp32" (tcgen05 kind::tf32 kernels with a hi/lo operand split, max-abs-err <= 1e-4).  Default from $VO2W_PRECISION, else "bf16".
     """
 
     def __init__(self, h, precision: str | None = None):
