@@ -252,3 +252,28 @@ def test_variance_adaptor_dropin_has_the_reference_state_dict_keys(tmp_path):
     va.eval()
     with pytest.raises(RuntimeError):           # no CPU fallback
         va(torch.zeros(1, 4, 256), torch.zeros(1, 4, dtype=torch.bool))
+
+
+def test_acoustic_tail_dropin_keys_and_errors(tmp_path):
+    """vtts.py:36-52: the four sub-modules behind the encoder under the reference's attribute names."""
+    import json
+    import visual_onoma_to_wave_b200 as v
+    from visual_onoma_to_wave_b200.synthetic import (seeded_variance_adaptor_state_dict, variance_model_config,
+                                                     seeded_decoder_state_dict, decoder_config, seeded_postnet_state_dict,
+                                                     VARIANCE_STATS)
+    (tmp_path / "stats.json").write_text(json.dumps(VARIANCE_STATS))
+    dkw = dict(n_layers=1, d_inner=64, kernels=(3, 1))
+    model_config = {**variance_model_config(), **decoder_config(**dkw)}
+    model_config["transformer"]["encoder_hidden"] = 256
+    pre_cfg = {"path": {"preprocessed": str(tmp_path)}, "preprocessing": {"mel": {"n_mel_channels": 80}}}
+    tail = v.AcousticTail(pre_cfg, model_config)
+    want = {"variance_adaptor." + k for k in seeded_variance_adaptor_state_dict(1)} | \
+           {"decoder." + k for k in seeded_decoder_state_dict(1, **dkw)} | \
+           {"postnet." + k for k in seeded_postnet_state_dict(1)} | {"mel_linear.weight", "mel_linear.bias"}
+    assert set(tail.state_dict().keys()) == want
+    tail.eval()
+    with pytest.raises(RuntimeError):           # no CPU fallback anywhere in the chain
+        tail(torch.zeros(1, 4, 256), torch.zeros(1, 4, dtype=torch.bool))
+    tail.train()
+    with pytest.raises(RuntimeError):           # inference only
+        tail(torch.zeros(1, 4, 256), torch.zeros(1, 4, dtype=torch.bool))

@@ -67,9 +67,17 @@ __host__ __device__ __forceinline__ float tf32_round(float v) {
 __device__ __forceinline__ void st_shared_f4(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// one instruction per element: nearest TF32, low 13 bits clear
+__device__ __forceinline__ float tf32_rna(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+// The staging loop is ALU-bound on the k = 1 layers, so the split is 2 instructions per element: hi = tf32(v), and
+// lo = v - hi is stored as it is (exact in fp32; the tensor pipe reads its top 19 bits, an error of 2^-21 |v|).
 __device__ __forceinline__ void split4(const float4& v, float4& hi, float4& lo) {
-    hi.x = tf32_round(v.x); hi.y = tf32_round(v.y); hi.z = tf32_round(v.z); hi.w = tf32_round(v.w);
-    lo.x = tf32_round(v.x - hi.x); lo.y = tf32_round(v.y - hi.y); lo.z = tf32_round(v.z - hi.z); lo.w = tf32_round(v.w - hi.w);
+    hi.x = tf32_rna(v.x); hi.y = tf32_rna(v.y); hi.z = tf32_rna(v.z); hi.w = tf32_rna(v.w);
+    lo.x = v.x - hi.x; lo.y = v.y - hi.y; lo.z = v.z - hi.z; lo.w = v.w - hi.w;
 }
 
 template <int NB>
@@ -120,10 +128,10 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
 #pragma unroll
             for (int i = 0; i < NRI; ++i) {
                 const int r = i * 32 + r_in, l = l0 - pad + r;
-                if (mine && r < p.R && l >= 0 && l < L) {
+                // nothing but the loads in this loop: they must all be in flight before the first one is consumed
+                if (mine && r < p.R && l >= 0 && l < L)
                     v[i] = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * ldx + c0 * T32_KC) + seg);
-                    v[i].x = lrelu(v[i].x, slope); v[i].y = lrelu(v[i].y, slope); v[i].z = lrelu(v[i].z, slope); v[i].w = lrelu(v[i].w, slope);
-                } else
+                else
                     v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             const int s0 = c0 % T32_AS, s1 = (c0 + 1) % T32_AS, use = c0 / T32_AS;      // c0 is even: same `use` for both
@@ -137,8 +145,11 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
                 for (int i = 0; i < NRI; ++i) {
                     const int r = i * 32 + r_in;
                     if (r < R8) {
-                        float4 hi, lo;
-                        split4(v[i], hi, lo);
+                        float4 t = v[i], hi, lo;
+                        if (slope != 1.f) {          // warp-uniform
+                            t.x = lrelu(t.x, slope); t.y = lrelu(t.y, slope); t.z = lrelu(t.z, slope); t.w = lrelu(t.w, slope);
+                        }
+                        split4(t, hi, lo);
                         st_shared_f4(base + (uint32_t)r * 16u, hi);
                         st_shared_f4(base + (uint32_t)(2 * R8 + r) * 16u, lo);
                     }
