@@ -1,4 +1,4 @@
 #!/bin/bash
 timeout 900 python -m pytest tests -q -m gpu -x 2>&1 | tail -3
-echo "--- current"; PYTHONPATH=. python tools/dec_err.py 2>&1 | tail -5
-python tools/fp32_mode_time.py 2>&1 | tail -2
+timeout 300 python __graft_entry__.py --smoke 2>&1 | tail -1
+python tools/launch_times.py 64 172 fp32 2>&1 | tail -2 | cut -c1-200

@@ -11,7 +11,8 @@ from visual_onoma_to_wave_b200.synthetic import V1_CONFIG, seeded_state_dict, sy
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 172
 dev = torch.device("cuda:0")
-g = v.Generator(v.AttrDict(V1_CONFIG), precision="bf16")
+PREC = sys.argv[3] if len(sys.argv) > 3 else "bf16"
+g = v.Generator(v.AttrDict(V1_CONFIG), precision=PREC)
 g.eval()
 g.remove_weight_norm()
 g.load_state_dict(seeded_state_dict(1234))

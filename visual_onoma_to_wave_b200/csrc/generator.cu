@@ -185,6 +185,35 @@ __global__ void __launch_bounds__(256) ups_as_conv_kernel(const float* __restric
     weff[e] = (t >= 0 && j < ks) ? w[((size_t)ci * Cout + co) * ks + j] : 0.f;
 }
 
+// conv_post of the fp32 mode on time-major input: wav[b,l] = tanh(bias + sum_{j,c} w[c,j] leaky_relu(x[b,l+j-pad,c], slope)).
+// One output channel, so no tensor-pipe tile: a CTA stages 256 + k - 1 frames (activated, rows padded to Cin + 1 floats
+// against bank conflicts) and every thread reduces its own frame window.
+__global__ void __launch_bounds__(256) post_conv_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                             const float* __restrict__ bias, float* __restrict__ wav, int L, int Cin,
+                                                             int k, float slope) {
+    extern __shared__ float psm[];
+    const int pad = (k - 1) / 2, rows = 256 + k - 1, ld = Cin + 1;
+    float* xs = psm;                    // [rows][ld]
+    float* ws = psm + rows * ld;        // [k][Cin]
+    const int b = blockIdx.y, l0 = blockIdx.x * 256;
+    const float* xb = x + (size_t)b * L * Cin;
+    for (int e = threadIdx.x; e < rows * Cin; e += 256) {
+        const int r = e / Cin, c = e - r * Cin, l = l0 - pad + r;
+        xs[r * ld + c] = (l >= 0 && l < L) ? lrelu(xb[(size_t)l * Cin + c], slope) : 0.f;
+    }
+    for (int e = threadIdx.x; e < k * Cin; e += 256) { const int j = e / Cin, c = e - j * Cin; ws[e] = w[c * k + j]; }   // w [1,Cin,k]
+    __syncthreads();
+    const int l = l0 + threadIdx.x;
+    if (l >= L) return;
+    float acc = bias[0];
+    for (int j = 0; j < k; ++j) {
+        const float* xr = xs + (threadIdx.x + j) * ld;
+        const float* wr = ws + j * Cin;
+        for (int c = 0; c < Cin; ++c) acc = fmaf(wr[c], xr[c], acc);
+    }
+    wav[(size_t)b * L + l] = tanhf(acc);
+}
+
 int pack_fp32_mode(vo2w_generator* g) {
     const vo2w_gen_config& cfg = g->cfg;
     size_t total = 0, bias_total = 0, scratch = 0;
@@ -489,17 +518,19 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
         L_in = s.L;
     }
     {
-        // conv_post: [B,L,C] -> [B,C,L], then the CUDA-core kernel (Cout = 1) with leaky-relu 0.01 in, tanh out
-        const StageBufs& s = p.st[g->n_stage - 1];
+        // conv_post (Cout = 1): leaky-relu 0.01 in, tanh out, straight from the time-major tensor
         const int idx = idx_conv_post(g);
         const LayerW& l = g->lw[idx];
-        VO2W_RUNK(0, rows_transpose_add(x_in, nullptr, f32(s.tt), B, (int)L_in, l.d1, st));
-        SimtConv q;
-        memset(&q, 0, sizeof(q));
-        q.B = B; q.stride = 1; q.div = 1.f;
-        q.x = f32(s.tt); q.w = g->w_dev + l.w_off; q.bias = Bi(idx); q.out = wav;
-        q.Cin = l.d1; q.Cout = 1; q.L = (int)L_in; q.k = l.k; q.dil = 1; q.pad = 3; q.in_slope = 0.01f; q.tanh_out = 1;
-        VO2W_RUN(simt_conv1d(q, st));
+        VO2W_REQUIRE(l.d0 == 1 && l.d1 <= 64 && l.k <= 11, "fp32 mode: conv_post %d -> %d, k %d unsupported", l.d1, l.d0, l.k);
+        const size_t smem = ((size_t)(256 + l.k - 1) * (l.d1 + 1) + (size_t)l.k * l.d1) * 4;
+        static bool attr = false;
+        if (!attr) {
+            VO2W_CUDA_OK(cudaFuncSetAttribute(post_conv_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+            attr = true;
+        }
+        dim3 grid((unsigned)vo2w_ceil_div(L_in, 256), (unsigned)B);
+        post_conv_rows_kernel<<<grid, 256, smem, st>>>(x_in, g->w_dev + l.w_off, Bi(idx), wav, (int)L_in, l.d1, l.k, 0.01f);
+        VO2W_RUN(cudaGetLastError() == cudaSuccess ? VO2W_OK : VO2W_E_CUDA);
     }
     return VO2W_OK;
 }
