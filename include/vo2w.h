@@ -224,6 +224,12 @@ int vo2w_duration_round(const float* log_duration, float d_control, float* out, 
  * Cout % 16 == 0. */
 int vo2w_debug_tf32_conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int L,
                          int Cin, int Cout, int k, int act, float* scratch, void* stream);
+/* The same with the fusions the Generator's fp32 mode uses (scripts/hifigan/models.py:96-103,156-163):
+ * out = act(out_scale * (bias + res + acc + sum_j W[:,:,j] leaky_relu(x[l + (j - (k-1)/2) * dil], in_slope))),
+ * dilation `dil` ((k-1)*dil <= 50), acc may alias out (the MRF sum), in_slope 1 = identity. */
+int vo2w_debug_tf32_conv_ex(const float* x, const float* w, const float* bias, const float* res, const float* acc,
+                            float* out, int B, int L, int Cin, int Cout, int k, int dil, float in_slope, float out_scale,
+                            int act, float* scratch, void* stream);
 
 /* ---- LengthRegulator -----------------------------------------------------------------
  * Replaces LengthRegulator.LR/expand (scripts/model/modules.py:132-155) + pad

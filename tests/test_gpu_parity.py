@@ -591,6 +591,35 @@ def test_tf32_split_convolution_is_fp32_accurate(dev, shape):
     assert err <= 4e-6 + 1e-8 * Cin * k, err
 
 
+TF32_FUSED = [  # B, L, C, k, dil     (ResBlock shapes of the Generator's fp32 mode, scripts/hifigan/models.py:96-103)
+    (2, 300, 128, 11, 5), (2, 700, 64, 7, 3), (3, 130, 32, 3, 5), (1, 1100, 32, 11, 5), (2, 257, 256, 3, 1),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", TF32_FUSED)
+def test_tf32_convolution_with_vocoder_fusions(dev, shape):
+    """Dilation, leaky-relu on the staged input, residual + in-place MRF accumulate, 1/num_kernels: against fp64."""
+    import torch.nn.functional as F
+    B, L, Cc, k, dil = shape
+    g = torch.Generator().manual_seed(Cc + k + dil)
+    x = torch.randn(B, L, Cc, generator=g)
+    w = torch.randn(Cc, Cc, k, generator=g) / (Cc * k) ** 0.5
+    bias, res, acc = torch.randn(Cc, generator=g), torch.randn(B, L, Cc, generator=g), torch.randn(B, L, Cc, generator=g)
+    y = F.conv1d(F.leaky_relu(x.double(), 0.1).transpose(1, 2), w.double(), bias.double(), padding=dil * (k - 1) // 2,
+                 dilation=dil).transpose(1, 2)
+    ref = (y + res.double() + acc.double()) / 3.0
+    xd, wd, bd, rd = x.to(dev), w.to(dev), bias.to(dev), res.to(dev)
+    out = acc.to(dev).clone()                     # acc aliases out, as xs += resblock(x) does
+    scratch = torch.empty(2 * w.numel(), device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().vo2w_debug_tf32_conv_ex(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), rd.data_ptr(), out.data_ptr(),
+                                                      out.data_ptr(), B, L, Cc, Cc, k, dil, 0.1, 1.0 / 3.0, 0, scratch.data_ptr(),
+                                                      torch.cuda.current_stream(dev).cuda_stream), "vo2w_debug_tf32_conv_ex")
+    err = float((out.cpu().double() - ref).abs().max())
+    assert err <= 4e-6 + 1e-8 * Cc * k, err
+
+
 def test_error_conventions(dev, gens):
     gen, _ = gens
     with pytest.raises(RuntimeError):

@@ -400,13 +400,20 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
 }
 
 // test / profiling entry: Conv1d weights [Cout,Cin,k] are packed on the fly into `scratch` (2*Cout*Cin*k floats)
-extern "C" int vo2w_debug_tf32_conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int L,
-                                    int Cin, int Cout, int k, int act, float* scratch, void* stream) {
+extern "C" int vo2w_debug_tf32_conv_ex(const float* x, const float* w, const float* bias, const float* res, const float* acc,
+                                       float* out, int B, int L, int Cin, int Cout, int k, int dil, float in_slope, float out_scale,
+                                       int act, float* scratch, void* stream) {
     VO2W_REQUIRE(x && w && out && scratch, "debug_tf32_conv: null argument");
     int rc = vo2w_device_check();
     if (rc != VO2W_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if ((rc = tf32_conv_pack(w, Cout, Cin, k, scratch, st)) != VO2W_OK) return rc;
     Tf32Conv c{x, scratch, bias, res, out, B, L, Cin, Cout, k, act};
+    c.dil = dil; c.in_slope = in_slope; c.acc = acc; c.out_scale = out_scale;
     return tf32_conv1d(c, st);
+}
+
+extern "C" int vo2w_debug_tf32_conv(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int L,
+                                    int Cin, int Cout, int k, int act, float* scratch, void* stream) {
+    return vo2w_debug_tf32_conv_ex(x, w, bias, res, nullptr, out, B, L, Cin, Cout, k, 1, 1.f, 1.f, act, scratch, stream);
 }
