@@ -380,7 +380,9 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     kp.n_t = tile_width(c.Cout, c.k);
     kp.n_tiles = c.Cout / kp.n_t;
     kp.chunks = c.Cin / T32_KC;
-    int NB = c.L > 256 ? 4 : (c.L > 128 ? 2 : 1);
+    // two row blocks at most: with 128-wide tiles that fills TMEM; narrower layers then fit two CTAs per SM, which hide
+    // each other's prologue / pipeline fill / epilogue (4 blocks per CTA: 49.1 ms for the vocoder's fp32 mode, 2: 45.1)
+    int NB = c.L > 128 ? 2 : 1;
     while (2 * NB * kp.n_t > 512) NB /= 2;
     // k = 1 layers are bound by the latency of the activation loads, not by the weight stream: half-size CTAs (two
     // per SM by registers, shared memory and TMEM columns) keep twice the loads in flight and hide each other's
@@ -394,7 +396,6 @@ int tf32_conv1d(const Tf32Conv& c, cudaStream_t st) {
     while (cols < (uint32_t)(2 * NB * kp.n_t)) cols *= 2;
     kp.tmem_cols = cols;
     const size_t smem = (size_t)T32_AS * kp.a_stage_bytes + (size_t)T32_WS * kp.w_stage_bytes;
-    if (NB == 4) return launch<4>(kp, smem, st);
     if (NB == 2) return launch<2>(kp, smem, st);
     return launch<1>(kp, smem, st);
 }
