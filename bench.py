@@ -27,7 +27,7 @@ import torch
 
 from visual_onoma_to_wave_b200.synthetic import (V1_CONFIG, FLOP_PER_FRAME, PAIR_FLOP_PER_FRAME, seeded_state_dict,
                                                  synthetic_mel)
-from visual_onoma_to_wave_b200.sharding import shard_bounds
+from visual_onoma_to_wave_b200.sharding import shard_bounds, max_over_ranks
 
 N_UTT, T_FRAMES, HOP, SR = 1024, 172, 256, 22050
 AUDIO_S_PER_UTT = T_FRAMES * HOP / SR
@@ -165,6 +165,90 @@ def lr_bandwidth(dev, peaks):
             "algorithmic_bytes": bytes_alg}
 
 
+def make_generator(v, precision, dev, sub):
+    gen = v.Generator(v.AttrDict(V1_CONFIG), precision=precision)
+    gen.eval()
+    with contextlib.redirect_stdout(sys.stderr):     # the reference prints here; stdout carries the JSON line only
+        gen.remove_weight_norm()
+    gen.load_state_dict(seeded_state_dict(1234))
+    gen.to(dev)
+    gen.host_sub_batch = sub
+    return gen
+
+
+def device_ms(fn, steps, warmup):
+    """CUDA-event time per call on torch's current stream (the stream the library launches on)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def tf32_peak(dev):
+    """TF32 tensor peak measured the way MEASURED_PEAKS.json measures bf16: torch.matmul 8192^3 with allow_tf32, best of
+    10 (burst) and back to back for 2 s (sustained).  BASELINE.md section 2 left this number to the builder."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev)
+        b = torch.randn(n, n, device=dev)
+        flops = 2.0 * n ** 3
+        for _ in range(3):
+            a @ b
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        reps = max(10, int(2000.0 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        sus = e0.elapsed_time(e1) / reps
+        return {"tf32_tflops": flops / best / 1e9, "tf32_tflops_sustained": flops / sus / 1e9,
+                "how": f"torch.matmul fp32 {n}^3 with allow_tf32=True: best of 10 (burst), {reps} back to back (sustained)"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def graph_ms(gen, mel, steps=10):
+    """One Generator.forward captured in a CUDA graph (the library's launches are plain stream work): ms per replay."""
+    side = torch.cuda.Stream(mel.device)
+    side.wait_stream(torch.cuda.current_stream(mel.device))
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            gen(mel)                      # warm-up on the capture stream: its workspace exists and is initialised
+    side.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        wav = gen(mel)
+    for _ in range(2):
+        graph.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        graph.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    del wav
+    return e0.elapsed_time(e1) / steps
+
+
 def run_ours(args):
     import torch.distributed as dist
     import visual_onoma_to_wave_b200 as v
@@ -179,36 +263,8 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
-
-    # weak scaling (default): every rank holds configs[3]'s 1024 utterances, the job is the 1024 * N utterance batch
-    # split contiguously; --scaling strong keeps the job at 1024 utterances in total
-    n_job = N_UTT * world if args.scaling == "weak" else N_UTT
-    lo, hi = shard_bounds(n_job, world, rank)
-    n_local = hi - lo
-    sub = min(args.sub_batch, n_local)
-    gen = v.Generator(v.AttrDict(V1_CONFIG), precision=args.precision)
-    gen.eval()
-    with contextlib.redirect_stdout(sys.stderr):     # the reference prints here; stdout carries the JSON line only
-        gen.remove_weight_norm()
-    gen.load_state_dict(seeded_state_dict(1234))
-    gen.to(dev)
-    gen.host_sub_batch = sub
-    mel_host = synthetic_mel(N_UTT, T_FRAMES, seed=0)[[i % N_UTT for i in range(lo, hi)]].contiguous().pin_memory()
-    mel_dev = mel_host.to(dev)
-    chunks = [(a, min(a + sub, n_local)) for a in range(0, n_local, sub)]
     cfg_m = {"vocoder": {"model": "HiFi-GAN"}}
-
-    def step_device():
-        out = None
-        for a, b in chunks:
-            out = gen(mel_dev[a:b])
-        return out
-
-    def step_e2e():
-        # public API, host buffers (utils/model.py:73-98): ONE vocoder_infer call over this rank's shard; the library
-        # walks it in sub-batches on two streams (pinned H2D, kernels, D2H overlapped) and returns numpy waveforms
-        wavs = v.vocoder_infer(mel_host, gen, cfg_m, {}, Normalize=False)
-        return len(wavs)
+    mel_all = synthetic_mel(N_UTT, T_FRAMES, seed=0)
 
     def barrier():
         if world > 1:
@@ -230,90 +286,164 @@ def run_ours(args):
         barrier()
         wall = time.perf_counter() - t0
         clocks = sampler.stop() if sampler else None
-        ms = torch.tensor([e0.elapsed_time(e1), wall * 1e3], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms[0]), float(ms[1]), clocks
+        ms = max_over_ranks([e0.elapsed_time(e1), wall * 1e3], dev)      # the job's time is its slowest rank's
+        return ms[0], ms[1], clocks
 
+    def run_job(gen, n_job, sub_batch, steps, warm, sampler=None):
+        """One job of n_job utterances split contiguously over the ranks: (device ms, e2e wall ms, clocks, shard info).
+        device: inputs resident in HBM, CUDA events; e2e: ONE vocoder_infer call over the rank's host mels (pinned), the
+        library walks them in sub-batches on two streams and copies every result straight into the caller's pinned
+        result buffer (utils/model.py:73-98: host mel in, numpy out)."""
+        lo, hi = shard_bounds(n_job, world, rank)
+        n_local = hi - lo
+        sub = max(1, min(sub_batch, n_local))
+        gen.host_sub_batch = sub
+        mel_host = mel_all[[i % N_UTT for i in range(lo, hi)]].contiguous().pin_memory()
+        mel_dev = mel_host.to(dev)
+        out_host = torch.empty(n_local, T_FRAMES * HOP).pin_memory()
+        chunks = [(a, min(a + sub, n_local)) for a in range(0, n_local, sub)]
+
+        def step_device():
+            out = None
+            for a, b in chunks:
+                out = gen(mel_dev[a:b])
+            return out
+
+        def step_e2e():
+            wavs = v.vocoder_infer(mel_host, gen, cfg_m, {}, Normalize=False, out=out_host)
+            return len(wavs)
+
+        dev_ms, _, clocks = timed(step_device, steps, warm, sampler)
+        launches = gen.last_launches * len(chunks)
+        _, e2e_ms, _ = timed(step_e2e, steps, 1)
+        return {"dev_ms": dev_ms / steps, "e2e_ms": e2e_ms / steps, "clocks": clocks, "n_local": n_local, "sub": sub,
+                "chunks": chunks, "launches": launches, "mel_dev": mel_dev}
+
+    # weak scaling (default): every rank holds configs[3]'s 1024 utterances, the job is the 1024 * N utterance batch
+    # split contiguously; --scaling strong keeps the job at 1024 utterances in total
+    n_job = N_UTT * world if args.scaling == "weak" else N_UTT
+    gen = make_generator(v, args.precision, dev, args.sub_batch)
     warm = max(args.warmup, 3)
-    dev_ms, _, clocks = timed(step_device, args.steps, warm, ClockSampler(local))
-    launches_per_step = gen.last_launches * len(chunks)
-    _, e2e_wall_ms, _ = timed(step_e2e, args.steps, 1)
-
+    job = run_job(gen, n_job, args.sub_batch, args.steps, warm, ClockSampler(local))
+    n_local, sub, chunks, mel_dev = job["n_local"], job["sub"], job["chunks"], job["mel_dev"]
+    launches_per_step = job["launches"]
     total_audio_s = n_job * AUDIO_S_PER_UTT
-    ms_per_step = dev_ms / args.steps
+    ms_per_step = job["dev_ms"]
     value = total_audio_s / (ms_per_step * 1e-3)
-    e2e_value = total_audio_s / (e2e_wall_ms / args.steps * 1e-3)
+    e2e_value = total_audio_s / (job["e2e_ms"] * 1e-3)
+    clocks = job["clocks"]
 
-    # roofline of the dominant kernel, pair_umma_kernel (28 of the 35 launches of a forward): its launches are timed
+    extra = {}
+    # configs[3] as BASELINE.json words it -- ONE 1024-utterance job split over the N GPUs (strong scaling) -- timed after
+    # the weak region at N > 1 (at N = 1 it is the headline itself)
+    if world > 1 and args.scaling == "weak":
+        sj = run_job(gen, N_UTT, args.sub_batch, args.steps, 2)
+        a_s = N_UTT * AUDIO_S_PER_UTT
+        extra["strong_scaling"] = {"utterances": N_UTT, "utterances_per_gpu": sj["n_local"], "sub_batch": sj["sub"],
+                                   "ms_per_step": sj["dev_ms"], "value": a_s / (sj["dev_ms"] * 1e-3), "unit": UNIT,
+                                   "e2e": {"value": a_s / (sj["e2e_ms"] * 1e-3), "unit": UNIT,
+                                           "h2d_bytes_per_step": N_UTT * 80 * T_FRAMES * 4, "d2h_bytes_per_step": N_UTT * T_FRAMES * HOP * 4},
+                                   "note": "the fixed 1024-utterance job of configs[3] split contiguously over the ranks; device time and "
+                                           "wall time are the max over ranks"}
+
+    # roofline of the dominant kernel, pair_umma_kernel (28 of the 34 launches of a forward): its launches are timed
     # live with CUDA events on the launching stream (vo2w_generator_set_timing), one sub-batch per pass, right after
     # the timed steps (GPU hot).  achieved = algorithmic FLOPs of those launches / their summed duration.
     a, b = chunks[0]
     pair_ms, all_ms, n_pair = 0.0, 0.0, 0
     passes = 3
+    kind_ms = {}
     if args.precision == "bf16":
         for _ in range(passes):
             ms_l, kinds = gen.launch_times(mel_dev[a:b])
             pair_ms += sum(m for m, k in zip(ms_l, kinds) if k == 2)
             all_ms += sum(ms_l)
             n_pair += sum(1 for k in kinds if k == 2)
+            for m, k in zip(ms_l, kinds):
+                kind_ms[k] = kind_ms.get(k, 0.0) + m
     if n_pair:
         flops_pair = PAIR_FLOP_PER_FRAME * (b - a) * T_FRAMES * passes
         achieved = flops_pair / (pair_ms * 1e-3) / 1e12
         per_launch = {"flops_per_launch": flops_pair / n_pair, "avg_launch_us": pair_ms * 1e3 / n_pair,
-                      "share_of_forward_time": pair_ms / all_ms, "launches_timed": n_pair}
+                      "share_of_forward_time": pair_ms / all_ms, "launches_timed": n_pair,
+                      "other_launches": {"single_conv_share_of_forward_time": kind_ms.get(1, 0.0) / all_ms,
+                                         "single_conv_us_per_forward": kind_ms.get(1, 0.0) * 1e3 / passes,
+                                         "what": "conv_pre + 4 upsamplers on stream_umma_kernel (conv_post rides the last fused launch)"}}
     else:   # fp32 mode: whole-step figure
         flops_local = FLOP_PER_FRAME * n_local * T_FRAMES
         achieved = flops_local / (ms_per_step * 1e-3) / 1e12
         per_launch = {"flops_per_launch": flops_local / launches_per_step, "avg_launch_us": ms_per_step * 1e3 / launches_per_step}
     peak = peaks["bf16_tflops_sustained"]
-    roofline = {"bound": "tensor", "kernel": "pair_umma_kernel (28 of the 35 launches of a forward, 96.8 % of its FLOPs)" if args.precision == "bf16" else "conv1d_f32_kernel",
+    roofline = {"bound": "tensor", "kernel": "pair_umma_kernel (28 of the 34 launches of a forward, 96.8 % of its FLOPs)" if args.precision == "bf16" else "tf32_conv_kernel",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": f"bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json (kernel timed inside a long step)",
+                "frac_of_burst_peak": achieved / peaks["bf16_tflops"],
                 "traffic": None, **per_launch}
+    # DRAM bytes per launch come from an `ncu --set full` capture and are only reported while that capture is of the
+    # kernel source being timed (sha256 of csrc/pair_umma.cu recorded next to it); otherwise null, never a stale constant
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof) and args.precision == "bf16":
-        try:   # ncu --set full capture at batch tj["batch"]; DRAM bytes scale linearly with the utterances of a launch
+        try:
+            import hashlib
             tj = json.load(open(prof))
-            roofline["traffic"] = tj["pair_umma_kernel_dram_bytes_per_launch"] * (b - a) / tj["batch"]
-            roofline["traffic_source"] = tj["source"]
+            src = os.path.join(ROOT, "visual_onoma_to_wave_b200", "csrc", "pair_umma.cu")
+            if tj.get("pair_umma_cu_sha256") == hashlib.sha256(open(src, "rb").read()).hexdigest():
+                roofline["traffic"] = tj["pair_umma_kernel_dram_bytes_per_launch"] * (b - a) / tj["batch"]
+                roofline["traffic_source"] = tj["source"]
+            else:
+                roofline["traffic_note"] = "null: the committed ncu capture (profiles/traffic.json) is of an older pair_umma.cu"
         except Exception:
             pass
 
-    extra = {}
     cpu_baseline = None
     if rank == 0:
         try:
             extra["length_regulator"] = lr_bandwidth(dev, peaks)
         except Exception as e:  # reported, not fatal for the vocoder metric
             extra["length_regulator"] = {"error": str(e)}
-        if world == 1 and args.precision == "bf16":
-            try:   # the exact mode (max-abs-err <= 1e-4 gate): same Generator on the tf32 hi/lo-split tensor-pipe kernel
-                g32 = v.Generator(v.AttrDict(V1_CONFIG), precision="fp32")
-                g32.eval()
-                with contextlib.redirect_stdout(sys.stderr):
-                    g32.remove_weight_norm()
-                g32.load_state_dict(seeded_state_dict(1234))
-                g32.to(dev)
-                m32 = mel_dev[:64]
-                for _ in range(2):
-                    g32(m32)
-                torch.cuda.synchronize(dev)
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                for _ in range(3):
-                    g32(m32)
-                e1.record()
-                torch.cuda.synchronize(dev)
-                ms32 = e0.elapsed_time(e1) / 3
-                nb = m32.shape[0]
-                extra["fp32_mode"] = {"utterances": nb, "ms": ms32, "audio_s_per_s": nb * T_FRAMES * 256 / 22050 / ms32 * 1e3,
-                                      "tflops_fp32_equivalent": FLOP_PER_FRAME * nb * T_FRAMES / ms32 / 1e9,
-                                      "kernel": "tf32_conv_kernel: tcgen05 kind::tf32, 3 products per fp32 product"}
+        if world == 1 and args.precision == "bf16" and not args.no_extras:
+            try:   # the exact mode (max-abs-err <= 1e-4 gate) on the FULL configs[3]: tcgen05 kind::tf32, hi/lo split
+                tp = tf32_peak(dev)
+                g32 = make_generator(v, "fp32", dev, 64)
+                j32 = run_job(g32, N_UTT, 64, 2, 1)
+                a_s = N_UTT * AUDIO_S_PER_UTT
+                eq = FLOP_PER_FRAME * N_UTT * T_FRAMES / (j32["dev_ms"] * 1e-3) / 1e12
+                extra["fp32_mode"] = {"utterances": N_UTT, "sub_batch": 64, "ms_per_step": j32["dev_ms"], "value": a_s / (j32["dev_ms"] * 1e-3),
+                                      "unit": UNIT, "e2e": {"value": a_s / (j32["e2e_ms"] * 1e-3), "unit": UNIT},
+                                      "tflops_fp32_equivalent": eq, "tflops_tf32_issued": 3 * eq,
+                                      "roofline": {"bound": "tensor", "achieved": 3 * eq, "peak": tp["tf32_tflops_sustained"], "unit": "TFLOP/s",
+                                                   "frac": 3 * eq / tp["tf32_tflops_sustained"], "frac_of_burst_peak": 3 * eq / tp["tf32_tflops"],
+                                                   "note": "whole forward; three TF32 products per fp32 product (hi.hi + lo.hi + hi.lo)"},
+                                      "tf32_peak": tp, "kernel": "tf32_conv_kernel: tcgen05 kind::tf32, 3 products per fp32 product"}
+                # configs[1]: B=16 x T=172, both modes, eager launches and one CUDA graph per forward
+                m16 = mel_dev[:16].contiguous()
+                c2 = {}
+                for name, gg in (("bf16", gen), ("fp32", g32)):
+                    ms_e = device_ms(lambda: gg(m16), 10, 3)
+                    try:
+                        ms_g = graph_ms(gg, m16)
+                    except Exception as e:
+                        ms_g = None
+                        c2[name + "_graph_error"] = str(e)
+                    a16 = 16 * AUDIO_S_PER_UTT
+                    c2[name] = {"ms": ms_e, "audio_s_per_s": a16 / (ms_e * 1e-3), "ms_cuda_graph": ms_g,
+                                "audio_s_per_s_cuda_graph": a16 / (ms_g * 1e-3) if ms_g else None, "launches": gg.last_launches}
+                extra["config2"] = {"workload": "configs[1]: HiFi-GAN V1 Generator forward, batch 16 x 2 s (T=172), device-resident", **c2}
                 del g32
+                torch.cuda.empty_cache()
+                # configs[4]: long-form, B=8 x T=2584 (30 s)
+                m5 = synthetic_mel(8, 2584, seed=5).to(dev)
+                ms5 = device_ms(lambda: gen(m5), 3, 2)
+                ws5 = int(_ws_bytes(gen, 8, 2584))
+                extra["config5"] = {"workload": "configs[4]: long-form synthesis, 30 s mels (T=2584) batch 8, bf16 mode, device-resident",
+                                    "ms": ms5, "audio_s_per_s": 8 * 2584 * HOP / SR / (ms5 * 1e-3), "workspace_bytes": ws5,
+                                    "tflops": FLOP_PER_FRAME * 8 * 2584 / (ms5 * 1e-3) / 1e12}
+                del m5
+                gen._ws.clear()
+                torch.cuda.empty_cache()
             except Exception as e:
-                extra["fp32_mode"] = {"error": str(e)}
-        if world == 1:
+                extra["extras_error"] = repr(e)
+        if world == 1 and not args.no_extras:
             try:   # SURVEY.md section 8 f1-f3: the acoustic tail in front of the vocoder, device timing per stage
                 sys.path.insert(0, os.path.join(ROOT, "tools"))
                 import bench_tail
@@ -339,7 +469,7 @@ def run_ours(args):
                        "l2": "no flush: each step streams >100 GB of activations per GPU through a 126 MB L2; inputs (56 MB) do not survive"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n_job * 80 * T_FRAMES * 4,
                     "d2h_bytes_per_step": n_job * T_FRAMES * HOP * 4,
-                    "api": "vocoder_infer(host mels of the whole shard) -> vo2w_generator_forward_host_async per sub-batch on two alternating streams (pinned H2D, kernels, D2H), numpy out, wall clock"},
+                    "api": "vocoder_infer(host mels of the whole shard, out=pinned result buffer) -> vo2w_generator_forward_host_async per sub-batch on two alternating streams (pinned H2D, kernels, D2H straight into the caller's buffer), numpy views out, wall clock"},
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
             "tflops": FLOP_PER_FRAME * n_job * T_FRAMES / (ms_per_step * 1e-3) / 1e12, "extra": extra,
@@ -348,6 +478,11 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def _ws_bytes(gen, B, T):
+    from visual_onoma_to_wave_b200 import _lib
+    return _lib.lib().vo2w_generator_workspace_bytes(gen._handle, B, T)
 
 
 def main():
@@ -360,6 +495,7 @@ def main():
     ap.add_argument("--sub-batch", type=int, default=128)
     ap.add_argument("--ref-utts", type=int, default=16, help="utterances per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip extra.fp32_mode / config2 / config5 / acoustic_tail")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: 1024 utterances per GPU (job = 1024 x N); strong: 1024 utterances in total")
     args = ap.parse_args()

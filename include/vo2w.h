@@ -15,6 +15,11 @@
  *     RuntimeError, which is the reference's only error convention).  vo2w_last_error()
  *     returns a thread-local message for the last failure.
  *   - there is no CPU fallback: without a CUDA device every compute call fails.
+ *   - threads: a handle's packed weights are read-only after create, but forward() also records
+ *     per-call state in the handle (launch count, timing events, the plan debug_tap reads), and a
+ *     workspace belongs to one in-flight forward.  So calls on ONE handle must be serialised by the
+ *     caller (the reference's callers are single-threaded Python); different
+ *     handles, and different devices, are independent.  Kernel attributes are set per device.
  */
 #ifndef VO2W_H
 #define VO2W_H
@@ -108,11 +113,15 @@ int vo2w_generator_forward_host_async(vo2w_generator* g, const float* mel_host, 
  * out_host as NCL [B,C,L].  Returns the element count, or a negative error. */
 long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap, float* out_host,
                                    size_t capacity);
+/* 1 when the last forward left the activation `tap` in its workspace (a tensor that a fused launch never
+ * writes to HBM has no tap), else 0. */
+int vo2w_generator_has_tap(const vo2w_generator* g, const char* tap);
 
 /* Known-answer probe: ONE reference layer through one kernel family, NCL fp32 in/out.
  * transposed = 0: nn.Conv1d(Cin, Cout, k, dilation=d, padding=d*(k-1)/2) (models.py:26-92)
  * transposed = 1: nn.ConvTranspose1d(Cin, Cout, k=2s, stride=s, padding=s/2) (models.py:123-135)
- * out = layer(leaky_relu(x, in_slope)) [+ res];  use_umma selects tcgen05 (1) or fp32 CUDA cores (0).
+ * out = layer(leaky_relu(x, in_slope)) [+ res];  use_umma selects fp32 CUDA cores (0), the tcgen05 single-CTA kernel
+ * (1) or the persistent tcgen05 CTA-pair kernel of the bf16 hot path (2; no residual).
  * w_host/bias_host in the torch layout, x/res/out on the device.  Synchronises `stream`. */
 int vo2w_debug_layer(int transposed, int use_umma, const float* w_host, const float* bias_host, int Cin,
                      int Cout, int k, int dil_or_stride, const float* x_dev, int B, int L, float in_slope,
@@ -132,6 +141,25 @@ int vo2w_debug_pair(int n_seg, const float* const* w1_host, const float* const* 
                     const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
                     const int* dils, int cg, const float* const* x_dev, int B, int L, float scale,
                     float out_slope, float* out_dev, float* act_dev, void* stream);
+
+/* The same launch with conv_post + tanh on board, as the last stage of Generator.forward runs it
+ * (scripts/hifigan/models.py:154-163): C = 32, CTA pairs;
+ *   wav = tanh(Conv1d(32, 1, 7, padding=3)(leaky_relu(y, out_slope)))  with y as above, in fp32 (y never reaches HBM);
+ * post_w_host [1,32,7] (torch layout).  wav_dev fp32 [B,L] and / or wav_i16_dev = (int16)(wav * i16_scale)
+ * (scripts/utils/model.py:83-86). */
+int vo2w_debug_pair_post(int n_seg, const float* const* w1_host, const float* const* b1_host,
+                         const float* const* w2_host, const float* const* b2_host, const int* ks, const int* dils,
+                         const float* const* x_dev, int B, int L, float scale, float out_slope,
+                         const float* post_w_host, float post_b, float* wav_dev, int16_t* wav_i16_dev,
+                         float i16_scale, void* stream);
+
+/* Host-only probe of the packing of stream_umma_kernel (conv_pre and the upsamplers of the bf16 mode, use_umma = 2 in
+ * vo2w_debug_layer): meta[0..15] = {Cin, Cout, up_s, KB, n_kb, NB, n_cols, n_tiles, n_items, halo_l, halo_r,
+ * stage_bytes, w_elems, bias_elems, 0, 0}, then item_shift[12], tile_shift[16]; w_out receives the packed bf16 bits
+ * [rank][tile][item][kb][KB/8][n_cols/2][8].  Pass w_out = NULL to query sizes. */
+int vo2w_debug_stream_pack(int transposed, const float* w, const float* bias, int Cin, int Cout, int k,
+                           int dil_or_stride, int32_t* meta, uint16_t* w_out, size_t w_capacity,
+                           float* bias_out, size_t bias_capacity);
 
 /* Host-only probe of the weight packing (no device needed): meta[0..11] = {Cin, Cout, n_cols,
  * n_tiles, phases_per_tile, halo_l, halo_r, n_items, w_tile_stride, up_s, w_elems, bias_elems},

@@ -83,6 +83,14 @@ def snr_db(ref: torch.Tensor, got: torch.Tensor) -> float:
     return float(10 * torch.log10(ref.pow(2).sum() / err.pow(2).sum().clamp_min(1e-300)))
 
 
+def ac_snr_db(ref: torch.Tensor, got: torch.Tensor) -> float:
+    """SNR against the AC power of the reference alone, 10 log10(sum (ref - mean ref)^2 / sum err^2): the error
+    is taken as it is (its own mean counts as error), only the reference's DC term is denied to the numerator."""
+    ref = ref.double()
+    err = got.double() - ref
+    return float(10 * torch.log10((ref - ref.mean()).pow(2).sum() / err.pow(2).sum().clamp_min(1e-300)))
+
+
 def generator_forward_emulated_v2(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float32, taps=None):
     """Dataflow of the pair-fused bf16 pipeline (DESIGN.md "Numerics"): every activation tensor
     that reaches HBM is raw bf16; leaky-relu is applied to the bf16 value and rounded to bf16 again
@@ -125,12 +133,18 @@ def generator_forward_emulated_v2(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float3
     return x.float()
 
 
-def generator_forward_emulated_v3(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float32, taps=None):
+def generator_forward_emulated_v3(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float32, taps=None, fused_post=True):
     """Dataflow of the single-stream bf16 pipeline: the ONLY tensor a layer leaves in HBM is
     s = bf16(leaky_relu(y_fp32, 0.1)), the next convolution's MMA operand.  A consumer that needs the
     value itself (the residual add of ResBlock.forward, models.py:102) recovers it exactly-invertibly
     from the stream: x = s if s >= 0 else 10 * s (an exact fp32 product of a bf16 number).  Compared with
-    v2 the operand is rounded once instead of twice and half of the HBM traffic disappears."""
+    v2 the operand is rounded once instead of twice and half of the HBM traffic disappears.
+
+    fused_post (the default schedule of the library): conv_post + tanh ride the last MRF launch, which holds
+    leaky_relu(xs / num_kernels, 0.01) in fp32 registers: conv_post then runs in fp32 on the unrounded tensor with fp32
+    weights (csrc/pair_umma.cu, POST) and "mrf_act.<last>" never exists.  fused_post=False restates the separate
+    conv_post launch (bf16 stream in, bf16 weights; VO2W_FUSE_POST=0)."""
+    sd_f32 = {k: v.float().to(acc_dtype) for k, v in fold_weight_norm(sd).items()}
     sd = fold_weight_norm(sd)
     W = {k: (_r(v.float(), "bf16") if k.endswith("weight") else v.float()).to(acc_dtype) for k, v in sd.items()}
     nk = len(cfg["resblock_kernel_sizes"])
@@ -159,9 +173,12 @@ def generator_forward_emulated_v3(sd, mel, cfg=V1_CONFIG, acc_dtype=torch.float3
                         sr = stream(r)
                 xs = r if xs is None else f32(xs + r)
             last = i + 1 == len(cfg["upsample_rates"])
+            if last and fused_post:
+                s = f32(F.leaky_relu(f32(xs * (1.0 / nk)), 0.01))
+                break
             s = stream(xs * (1.0 / nk), 0.01 if last else LRELU_SLOPE)
             if taps is not None:
                 taps[f"mrf_act.{i}"] = s.float()
-        x = f32(F.conv1d(s, W["conv_post.weight"], W["conv_post.bias"], padding=3))
+        x = f32(F.conv1d(s, (sd_f32 if fused_post else W)["conv_post.weight"], W["conv_post.bias"], padding=3))
         x = torch.tanh(x)
     return x.float()

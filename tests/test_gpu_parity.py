@@ -131,10 +131,12 @@ LAYERS = [  # transposed, Cin, Cout, k, dil|stride, L, B, in_slope, residual
 ]
 
 
-@pytest.mark.parametrize("umma", [0, 1], ids=["simt", "umma"])
+@pytest.mark.parametrize("umma", [0, 1, 2], ids=["simt", "umma", "stream"])
 @pytest.mark.parametrize("case", LAYERS, ids=lambda c: "-".join(str(i) for i in c))
 def test_single_layer_against_torch(dev, case, umma):
     tr, Cin, Cout, k, ds, L, B, slope, use_res = case
+    if umma == 2 and use_res:
+        pytest.skip("stream_umma_kernel (conv_pre / upsamplers) has no residual input")
     g = torch.Generator().manual_seed(Cin * 31 + k)
     w = torch.randn((Cin, Cout, k) if tr else (Cout, Cin, k), generator=g) / (Cin * k) ** 0.5
     b = torch.randn(Cout, generator=g) * 0.1
@@ -156,6 +158,40 @@ def test_single_layer_against_torch(dev, case, umma):
     if use_res:
         ref = ref + res.double()
     err = float((out.cpu().double() - ref).abs().max())
+    assert err < 3e-5, err
+
+
+STREAM_SHAPES = [  # transposed, Cin, Cout, k, dil|stride, L, B: shapes where a persistent CTA pair walks SEVERAL units
+    (1, 512, 256, 16, 8, 172, 40),    # ups[0]: input tile single-buffered, weights streamed, N-tile groups
+    (1, 256, 128, 16, 8, 1400, 16),   # ups[1]: two row blocks per CTA, ragged last tile
+    (1, 128, 64, 4, 2, 6000, 8),      # ups[2]: weights resident in the ring, double-buffered input
+    (1, 64, 32, 4, 2, 9000, 11),      # ups[3]: four row blocks per CTA, odd number of tiles (dead tile in the last pair)
+    (0, 80, 512, 7, 1, 172, 20),      # conv_pre
+    (0, 32, 64, 3, 1, 70000, 1),      # one long utterance
+]
+
+
+@pytest.mark.parametrize("case", STREAM_SHAPES, ids=lambda c: "-".join(str(i) for i in c))
+def test_stream_kernel_over_many_units(dev, case):
+    """stream_umma_kernel (models.py:118-135,150-153) where every pair runs its persistent loop more than once: ring
+    phases, accumulator / input buffer alternation, N-tile groups and the tile tail are all exercised."""
+    tr, Cin, Cout, k, ds, L, B = case
+    g = torch.Generator().manual_seed(Cin * 13 + Cout + L)
+    w = torch.randn((Cin, Cout, k) if tr else (Cout, Cin, k), generator=g) / (Cin * (2 if tr else k)) ** 0.5
+    b = torch.randn(Cout, generator=g) * 0.1
+    x = torch.randn(B, Cin, L, generator=g)
+    out = torch.full((B, Cout, L * (ds if tr else 1)), float("nan"), device=dev)
+    xd = x.to(dev)
+    _lib.check(_lib.lib().vo2w_debug_layer(tr, 2, w.data_ptr(), b.data_ptr(), Cin, Cout, k, ds, xd.data_ptr(), B, L, 0.1, None,
+                                           out.data_ptr(), None))
+    xa, wr = F.leaky_relu(x, 0.1).to(torch.bfloat16).double(), w.to(torch.bfloat16).double()
+    if tr:
+        ref = F.conv_transpose1d(xa, wr, b.double(), stride=ds, padding=(k - ds) // 2)
+    else:
+        ref = F.conv1d(xa, wr, b.double(), padding=ds * (k - 1) // 2, dilation=ds)
+    got = out.cpu().double()
+    assert torch.isfinite(got).all()
+    err = float((got - ref).abs().max())
     assert err < 3e-5, err
 
 
@@ -211,6 +247,47 @@ def test_fused_resblock_iterations_against_torch(dev, case):
     assert int(((got - aref).abs() > tol).sum()) == 0, float((got - aref).abs().max())
     inv = torch.where(got < 0, got / slope, got)
     assert float((out.cpu().double() - inv).abs().max()) <= 1e-5 * float(inv.abs().max())
+
+
+POST_CASES = [  # kernel sizes, dilations, B, L       (32 channels, CTA pairs; a tile is responsible for 496 samples)
+    ([3, 7, 11], [5, 5, 5], 3, 2000), ([3, 7, 11], [5, 5, 5], 2, 496), ([3, 7, 11], [5, 5, 5], 2, 497), ([3, 7, 11], [5, 5, 5], 1, 50),
+    ([3, 7, 11], [5, 5, 5], 5, 44032), ([7], [3], 2, 1300), ([3], [1], 2, 3), ([3, 7, 11], [1, 3, 5], 1, 995),
+]
+
+
+@pytest.mark.parametrize("case", POST_CASES, ids=lambda c: f"k{'_'.join(map(str, c[0]))}-B{c[2]}-L{c[3]}")
+def test_mrf_launch_with_conv_post_on_board(dev, case):
+    """The last launch of Generator.forward (models.py:154-163): MRF sum / average, leaky_relu(0.01), conv_post, tanh in
+    one kernel; the 32-channel tensor never reaches HBM.  Reference: the SAME launch without conv_post (its bf16 stream,
+    tested above), conv_post + tanh applied in torch fp64; the stream's bf16 rounding (which the fused path does not have)
+    bounds the difference.  The int16 output must be the float output truncated."""
+    import ctypes as C
+    ks, ds, B, L = case
+    n = len(ks)
+    g = torch.Generator().manual_seed(100 + L)
+    w1 = [(torch.randn(32, 32, k, generator=g) / (32 * k) ** 0.5).contiguous() for k in ks]
+    w2 = [(torch.randn(32, 32, k, generator=g) / (32 * k) ** 0.5).contiguous() for k in ks]
+    b1 = [torch.randn(32, generator=g) * 0.1 for _ in ks]
+    b2 = [torch.randn(32, generator=g) * 0.1 for _ in ks]
+    pw = (torch.randn(1, 32, 7, generator=g) / 224 ** 0.5).contiguous()
+    pb = 0.05
+    xd = [torch.randn(B, 32, L, generator=g).to(dev) for _ in ks]
+    pa = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    kk, dd = (C.c_int * n)(*ks), (C.c_int * n)(*ds)
+    act = torch.full((B, 32, L), float("nan"), device=dev)
+    lib = _lib.lib()
+    _lib.check(lib.vo2w_debug_pair(n, pa(w1), pa(b1), pa(w2), pa(b2), 32, kk, dd, 2, pa(xd), B, L, 1.0 / n, 0.01, None,
+                                   act.data_ptr(), None))
+    wav = torch.full((B, L), float("nan"), device=dev)
+    i16 = torch.full((B, L), -12345, device=dev, dtype=torch.int16)
+    _lib.check(lib.vo2w_debug_pair_post(n, pa(w1), pa(b1), pa(w2), pa(b2), kk, dd, pa(xd), B, L, 1.0 / n, 0.01, pw.data_ptr(), pb,
+                                        wav.data_ptr(), i16.data_ptr(), 32768.0, None))
+    ref = torch.tanh(F.conv1d(act.cpu().double(), pw.double(), torch.tensor([pb]).double(), padding=3))[:, 0]
+    got = wav.cpu()
+    assert torch.isfinite(got).all()
+    err = float((got.double() - ref).abs().max())
+    assert err <= 5e-3, err
+    assert torch.equal(i16.cpu(), torch.from_numpy((got.numpy() * np.float32(32768.0)).astype("int16")))
 
 
 # ------------------------------------------------------------------------------------------

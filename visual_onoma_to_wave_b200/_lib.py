@@ -42,6 +42,7 @@ SYMBOLS = {
                                                     C.c_float, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
                                                     C.c_void_p]),
     "vo2w_generator_debug_tap": (C.c_longlong, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t]),
+    "vo2w_generator_has_tap": (C.c_int, [C.c_void_p, C.c_char_p]),
     "vo2w_debug_layer": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                    C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vo2w_debug_pack": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
@@ -49,6 +50,11 @@ SYMBOLS = {
     "vo2w_debug_pair": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                   C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                   C.c_void_p]),
+    "vo2w_debug_pair_post": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_float, C.c_void_p,
+                                       C.c_void_p, C.c_float, C.c_void_p]),
+    "vo2w_debug_stream_pack": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "vo2w_generator_last_launches": (C.c_int, [C.c_void_p]),
     "vo2w_generator_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "vo2w_generator_get_timing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),

@@ -35,6 +35,16 @@ void vo2w_set_error(const char* fmt, ...);
 
 static inline int vo2w_ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// One-time per-DEVICE setup (cudaFuncSetAttribute, SM count): function attributes belong to the device's context, so a
+// process that drives several GPUs must set them once per device, not once per process.
+#define VO2W_MAX_DEV 64
+static inline int vo2w_cur_dev() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return (d >= 0 && d < VO2W_MAX_DEV) ? d : 0;
+}
+int vo2w_sm_count();   // errors.cu: multiprocessors of the current device (cached per device)
+
 // ---------------------------------------------------------------------------------------
 // activation layouts (DESIGN.md "Data layout in HBM")
 //

@@ -323,10 +323,11 @@ int tile_width(int Cout, int k) {
 
 template <int NB>
 int launch(const T32K& kp, size_t smem, cudaStream_t st) {
-    static bool attr = false;
-    if (!attr) {
+    static bool attr[VO2W_MAX_DEV];
+    const int cur = vo2w_cur_dev();
+    if (!attr[cur]) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(tf32_conv_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-        attr = true;
+        attr[cur] = true;
     }
     dim3 grid((unsigned)vo2w_ceil_div(kp.c.L, 128 * NB), (unsigned)kp.n_tiles, (unsigned)(kp.c.B * kp.c.heads));
     tf32_conv_kernel<NB><<<grid, T32_THREADS, smem, st>>>(kp);

@@ -239,10 +239,11 @@ __global__ void chunk_f32_kernel(const float* __restrict__ x, float* __restrict_
 size_t umma_conv_smem(const UConv& p) { return (size_t)p.a_bytes + (size_t)UMMA_STAGES * p.stage_bytes; }
 
 int umma_conv_launch(const UConv& p, int m_tiles, int n_tiles, int B, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[VO2W_MAX_DEV];
+    const int cur = vo2w_cur_dev();
+    if (!attr_set[cur]) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(umma_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, UMMA_SMEM_LIMIT));
-        attr_set = true;
+        attr_set[cur] = true;
     }
     const size_t smem = umma_conv_smem(p);
     VO2W_REQUIRE(smem <= UMMA_SMEM_LIMIT, "umma conv: %zu bytes of shared memory exceed the limit", smem);

@@ -250,10 +250,11 @@ int rows_layernorm_mask(const float* x, const float* gamma, const float* beta, c
 
 int rows_attention(const float* qkv, const uint8_t* mask, float* out, int B, int L, int D, int n_head, cudaStream_t st) {
     VO2W_REQUIRE(D == n_head * AD, "attention: head size must be %d (d_model %d, heads %d)", AD, D, n_head);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[VO2W_MAX_DEV];
+    const int cur = vo2w_cur_dev();
+    if (!attr_set[cur]) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATTN_SMEM));
-        attr_set = true;
+        attr_set[cur] = true;
     }
     dim3 grid((unsigned)vo2w_ceil_div(L, AQ), (unsigned)n_head, (unsigned)B);
     attention_kernel<<<grid, 256, ATTN_SMEM, st>>>(qkv, mask, out, L, D, 1.0f / sqrtf((float)AD));

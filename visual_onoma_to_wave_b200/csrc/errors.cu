@@ -13,6 +13,17 @@ void vo2w_set_error(const char* fmt, ...) {
 extern "C" const char* vo2w_last_error(void) { return g_err; }
 extern "C" int vo2w_version(void) { return 100; }
 
+int vo2w_sm_count() {
+    static int n_sms[VO2W_MAX_DEV];
+    const int dev = vo2w_cur_dev();
+    if (!n_sms[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        n_sms[dev] = n;
+    }
+    return n_sms[dev];
+}
+
 extern "C" int vo2w_device_check(void) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) {

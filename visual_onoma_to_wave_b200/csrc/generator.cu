@@ -18,6 +18,7 @@
 #include "rows.cuh"
 #include "pack.cuh"
 #include "pair_umma.cuh"
+#include "stream_umma.cuh"
 
 namespace {
 
@@ -42,6 +43,8 @@ struct StageBufs {         // per upsampling stage, offsets in bytes into the wo
 struct Plan {
     int B = 0, T = 0;
     size_t melb = 0, a0 = 0, c0_f32 = 0;
+    size_t i16 = 0;                // int16 PCM staging of the host path (its own region: the operand buffers' zero pad
+                                   // rows are an invariant between forwards, so nothing may be staged on top of them)
     StageBufs st[4];
     size_t total = 0;
 };
@@ -63,7 +66,12 @@ struct vo2w_generator {
     float* ups_bias = nullptr;     // bias replicated per phase, ups_bias_off[i]
     size_t ups_bias_off[4] = {};
     // bf16 mode
-    PackedLayer conv_pre, conv_post, ups[4];
+    PackedLayer conv_pre, conv_post, ups[4];   // umma_conv_kernel packing (conv_post when it is not fused; A/B fallback)
+    SuLayer s_pre, s_ups[4];       // stream_umma_kernel packing: conv_pre and the upsamplers on persistent CTA pairs
+    bool use_stream = true;        // VO2W_SINGLE_CONV=old selects umma_conv_kernel for conv_pre / ups (A/B runs)
+    bool fuse_post = false;        // conv_post + tanh ride the last stage's MRF launch (32 channels, k = 7, CTA pairs)
+    float post_w[PAIR_POST_K * 32] = {};   // conv_post weights [tap][channel] fp32
+    float post_b = 0.f;
     PackedPair pairs[12][3];       // resblocks[n] iteration m: convs1[m] + convs2[m]
     PackedGroup iter_group[12][2]; // one launch = iteration m < 2 of resblocks[n]
     PackedGroup mrf_group[4];      // one launch = last iteration of all ResBlocks of a stage + the MRF average
@@ -72,6 +80,7 @@ struct vo2w_generator {
     Plan last;
     void* last_ws = nullptr;
     int last_launches = 0;
+    bool last_fused_post = false;  // the last forward ran conv_post inside the last MRF launch ("mrf_act.<last>" was never written)
     // optional per-launch device timing (vo2w_generator_set_timing): events around every launch of a forward
     bool timing = false;
     std::vector<cudaEvent_t> ev;
@@ -133,6 +142,9 @@ Plan make_plan(const vo2w_generator* g, int B, int T) {
             s.xs = take(f32b);
         }
     }
+    long long hop = 1;
+    for (int i = 0; i < g->n_stage; ++i) hop *= g->cfg.upsample_rates[i];
+    p.i16 = take((size_t)B * T * hop * 2);
     p.total = off;
     return p;
 }
@@ -306,10 +318,30 @@ extern "C" int vo2w_generator_create(const vo2w_gen_config* cfg, const float* we
         VO2W_TRY(pc(g->conv_post, idx_conv_post(g), 1));
         const char* cge = getenv("VO2W_PAIR_CG");
         g->pair_cg = (cge && cge[0] == '1') ? 1 : 2;
+        const char* sce = getenv("VO2W_SINGLE_CONV");
+        g->use_stream = !(sce && sce[0] == 'o');
+        {
+            const LayerW& l = g->lw[idx_conv_pre()];
+            VO2W_TRY(su_pack_conv(g->s_pre, W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, 1));
+            VO2W_TRY(su_upload(g->s_pre));
+            // conv_post can ride the last MRF launch when that launch is the 32-channel CTA-pair kernel and the layer
+            // is the reference's Conv1d(32, 1, 7, padding=3).  VO2W_FUSE_POST=0 or debug taps keep it a launch of its own.
+            const LayerW& lp = g->lw[idx_conv_post(g)];
+            const char* fpe = getenv("VO2W_FUSE_POST");
+            g->fuse_post = g->pair_cg == 2 && lp.d0 == 1 && lp.d1 == 32 && lp.k == PAIR_POST_K && stage_channels(g, g->n_stage - 1) == 32 &&
+                           !(fpe && fpe[0] == '0') && !g->debug_taps;
+            if (lp.d0 == 1 && lp.d1 == 32 && lp.k == PAIR_POST_K) {
+                for (int c = 0; c < 32; ++c)
+                    for (int j = 0; j < PAIR_POST_K; ++j) g->post_w[j * 32 + c] = W[lp.w_off + (size_t)c * PAIR_POST_K + j];
+                g->post_b = W[lp.b_off];
+            }
+        }
         for (int i = 0; i < g->n_stage; ++i) {
             const LayerW& l = g->lw[idx_ups(i)];
             VO2W_TRY(pack_convT(g->ups[i], W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, cfg->upsample_rates[i]));
             VO2W_TRY(upload_layer(g->ups[i]));
+            VO2W_TRY(su_pack_convT(g->s_ups[i], W + l.w_off, W + l.b_off, l.d0, l.d1, l.k, cfg->upsample_rates[i]));
+            VO2W_TRY(su_upload(g->s_ups[i]));
             const int ch = stage_channels(g, i);
             for (int j = 0; j < g->nk; ++j) {
                 const int n = i * g->nk + j;
@@ -343,7 +375,8 @@ extern "C" int vo2w_generator_destroy(vo2w_generator* g) {
     for (cudaEvent_t e : g->ev) cudaEventDestroy(e);
     free_layer(g->conv_pre);
     free_layer(g->conv_post);
-    for (int i = 0; i < 4; ++i) free_layer(g->ups[i]);
+    su_free(g->s_pre);
+    for (int i = 0; i < 4; ++i) { free_layer(g->ups[i]); su_free(g->s_ups[i]); }
     for (int i = 0; i < 4; ++i) free_group(g->mrf_group[i]);
     for (int n = 0; n < 12; ++n) {
         for (int m = 0; m < 2; ++m) free_group(g->iter_group[n][m]);
@@ -402,25 +435,34 @@ int mark_launch(vo2w_generator* g, int kind, cudaStream_t st) {
 #define VO2W_RUN(expr) VO2W_RUNK(1, expr)
 
 // Generator.forward (models.py:149-165) on the tcgen05 path.
-int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, uint8_t* ws, cudaStream_t st) {
+int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, short* wav_i16, float i16_scale, uint8_t* ws,
+                 cudaStream_t st) {
     const int B = p.B, T = p.T;
     auto bf = [&](size_t off) { return (__nv_bfloat16*)(ws + off); };
+    const bool fused_post = g->fuse_post;
+    g->last_fused_post = fused_post;
 
     // mel [B,80,T] fp32 -> operand buffer
     VO2W_RUNK(0, pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
     {   // x = conv_pre(mel); the only consumer is leaky_relu(0.1) -> ups[0]
-        const PackedLayer* L[1] = {&g->conv_pre};
-        const __nv_bfloat16* in[1] = {bf(p.melb)};
-        EpilogueSpec ep;
-        ep.out_bf16 = bf(p.a0);
-        ep.out_slope = 0.1f;
-        VO2W_RUN(launch_layers(L, in, 1, B, T, ep, st));
+        if (g->use_stream) {
+            VO2W_RUN(su_launch(g->s_pre, bf(p.melb), bf(p.a0), nullptr, 0.1f, B, T, st));
+        } else {
+            const PackedLayer* L[1] = {&g->conv_pre};
+            const __nv_bfloat16* in[1] = {bf(p.melb)};
+            EpilogueSpec ep;
+            ep.out_bf16 = bf(p.a0);
+            ep.out_slope = 0.1f;
+            VO2W_RUN(launch_layers(L, in, 1, B, T, ep, st));
+        }
     }
     const __nv_bfloat16* stage_in = bf(p.a0);
     long long L_in = T;
     for (int i = 0; i < g->n_stage; ++i) {
         const StageBufs& s = p.st[i];
-        {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM; writes the stream x and leaky_relu(x), both bf16
+        if (g->use_stream) {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM on persistent CTA pairs
+            VO2W_RUN(su_launch(g->s_ups[i], stage_in, bf(s.xa), nullptr, 0.1f, B, (int)L_in, st));
+        } else {
             const PackedLayer* L[1] = {&g->ups[i]};
             const __nv_bfloat16* in[1] = {stage_in};
             EpilogueSpec ep;
@@ -449,12 +491,22 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
             io.out_act = bf(s.mrf);
             io.out_slope = next_slope;
             io.scale = 1.0f / (float)g->nk;
+            if (fused_post && i + 1 == g->n_stage) {
+                // ... and wav = tanh(conv_post(leaky_relu(x, 0.01))) (models.py:161-163) in the same launch: the
+                // 32-channel tensor x is never written to HBM
+                io.out_act = nullptr;
+                io.post_w = g->post_w;
+                io.post_b = g->post_b;
+                io.wav = wav;
+                io.wav_i16 = wav_i16;
+                io.i16_scale = i16_scale;
+            }
             VO2W_RUNK(2, pair_launch(g->mrf_group[i], io, B, (int)s.L, st));
         }
         stage_in = bf(s.mrf);
         L_in = s.L;
     }
-    {   // wav = tanh(conv_post(leaky_relu(x)))
+    if (!fused_post) {   // wav = tanh(conv_post(leaky_relu(x)))
         const PackedLayer* L[1] = {&g->conv_post};
         const __nv_bfloat16* in[1] = {stage_in};
         EpilogueSpec ep;
@@ -523,10 +575,11 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
         const LayerW& l = g->lw[idx];
         VO2W_REQUIRE(l.d0 == 1 && l.d1 <= 64 && l.k <= 11, "fp32 mode: conv_post %d -> %d, k %d unsupported", l.d1, l.d0, l.k);
         const size_t smem = ((size_t)(256 + l.k - 1) * (l.d1 + 1) + (size_t)l.k * l.d1) * 4;
-        static bool attr = false;
-        if (!attr) {
+        static bool attr[VO2W_MAX_DEV];
+        const int cur = vo2w_cur_dev();
+        if (!attr[cur]) {
             VO2W_CUDA_OK(cudaFuncSetAttribute(post_conv_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-            attr = true;
+            attr[cur] = true;
         }
         dim3 grid((unsigned)vo2w_ceil_div(L_in, 256), (unsigned)B);
         post_conv_rows_kernel<<<grid, 256, smem, st>>>(x_in, g->w_dev + l.w_off, Bi(idx), wav, (int)L_in, l.d1, l.k, 0.01f);
@@ -537,8 +590,17 @@ int forward_fp32(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
 
 }  // namespace
 
-extern "C" int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B, int T, float* wav, void* workspace,
-                                      size_t workspace_bytes, int ws_fresh, void* stream) {
+namespace {
+__global__ void wav_to_i16_kernel(const float* __restrict__ w, short* __restrict__ o, float scale, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = (short)(int)(w[i] * scale);   // numpy astype("int16") of in-range floats truncates toward zero
+}
+}  // namespace
+
+// Generator.forward with an optional int16 copy of the waveform, (int16)(wav * i16_scale) as utils/model.py:83-86 makes
+// it: written by the last launch itself where conv_post rides the MRF launch, else by a conversion kernel.
+static int forward_impl(vo2w_generator* g, const float* mel, int B, int T, float* wav, short* wav_i16, float i16_scale,
+                        void* workspace, size_t workspace_bytes, int ws_fresh, void* stream) {
     VO2W_REQUIRE(g && mel && wav, "generator_forward: null argument");
     VO2W_REQUIRE(B > 0 && T > 0, "generator_forward: empty batch (B=%d T=%d)", B, T);
     VO2W_REQUIRE(B <= 65535, "generator_forward: batch %d exceeds grid.z", B);
@@ -563,16 +625,30 @@ extern "C" int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B
     }
     if (ws_fresh && g->precision == VO2W_PREC_BF16)   // halo / tail rows of the operand buffers must read as zero
         VO2W_CUDA_OK(cudaMemsetAsync(workspace, 0, p.total, st));
-    if (g->precision == VO2W_PREC_BF16) return forward_bf16(g, p, mel, wav, (uint8_t*)workspace, st);
-    return forward_fp32(g, p, mel, wav, (uint8_t*)workspace, st);
+    int rc;
+    if (g->precision == VO2W_PREC_BF16) {
+        rc = forward_bf16(g, p, mel, wav, wav_i16, i16_scale, (uint8_t*)workspace, st);
+        if (rc != VO2W_OK || g->last_fused_post) return rc;
+    } else {
+        g->last_fused_post = false;
+        rc = forward_fp32(g, p, mel, wav, (uint8_t*)workspace, st);
+        if (rc != VO2W_OK) return rc;
+    }
+    if (wav_i16) {
+        long long hop = 1;
+        for (int i = 0; i < g->n_stage; ++i) hop *= g->cfg.upsample_rates[i];
+        const long long n_out = (long long)B * T * hop;
+        wav_to_i16_kernel<<<(unsigned)vo2w_ceil_div(n_out, 256), 256, 0, st>>>(wav, wav_i16, i16_scale, n_out);
+        VO2W_CUDA_OK(cudaGetLastError());
+        ++g->last_launches;
+    }
+    return VO2W_OK;
 }
 
-namespace {
-__global__ void wav_to_i16_kernel(const float* __restrict__ w, short* __restrict__ o, float scale, long long n) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) o[i] = (short)(int)(w[i] * scale);   // numpy astype("int16") of in-range floats truncates toward zero
+extern "C" int vo2w_generator_forward(vo2w_generator* g, const float* mel, int B, int T, float* wav, void* workspace,
+                                      size_t workspace_bytes, int ws_fresh, void* stream) {
+    return forward_impl(g, mel, B, T, wav, nullptr, 0.f, workspace, workspace_bytes, ws_fresh, stream);
 }
-}  // namespace
 
 static int forward_host_impl(vo2w_generator* g, const float* mel_host, int B, int T, float* wav_host,
                              int16_t* wav_i16_host, float max_wav_value, void* workspace, size_t workspace_bytes,
@@ -585,18 +661,12 @@ static int forward_host_impl(vo2w_generator* g, const float* mel_host, int B, in
     for (int i = 0; i < g->n_stage; ++i) up *= g->cfg.upsample_rates[i];
     const long long n_out = (long long)B * T * up;
     VO2W_CUDA_OK(cudaMemcpyAsync(mel_dev, mel_host, (size_t)B * 80 * T * 4, cudaMemcpyHostToDevice, st));
-    int rc = vo2w_generator_forward(g, (const float*)mel_dev, B, T, (float*)wav_dev, workspace, workspace_bytes, ws_fresh,
-                                    stream);
+    // int16 samples are staged in their own region of the workspace (Plan::i16), never over the operand buffers
+    short* i16_dev = wav_i16_host ? (short*)((uint8_t*)workspace + make_plan(g, B, T).i16) : nullptr;
+    int rc = forward_impl(g, (const float*)mel_dev, B, T, (float*)wav_dev, i16_dev, max_wav_value, workspace, workspace_bytes,
+                          ws_fresh, stream);
     if (rc != VO2W_OK) return rc;
-    if (wav_i16_host) {
-        // int16 samples reuse the head of the workspace (the mel operand buffer is dead by now)
-        VO2W_REQUIRE((size_t)n_out * 2 <= workspace_bytes, "generator_forward_host: workspace too small for int16");
-        wav_to_i16_kernel<<<(unsigned)vo2w_ceil_div(n_out, 256), 256, 0, st>>>((const float*)wav_dev, (short*)workspace,
-                                                                              max_wav_value, n_out);
-        VO2W_CUDA_OK(cudaGetLastError());
-        ++g->last_launches;
-        VO2W_CUDA_OK(cudaMemcpyAsync(wav_i16_host, workspace, (size_t)n_out * 2, cudaMemcpyDeviceToHost, st));
-    }
+    if (wav_i16_host) VO2W_CUDA_OK(cudaMemcpyAsync(wav_i16_host, i16_dev, (size_t)n_out * 2, cudaMemcpyDeviceToHost, st));
     if (wav_host) VO2W_CUDA_OK(cudaMemcpyAsync(wav_host, wav_dev, (size_t)n_out * 4, cudaMemcpyDeviceToHost, st));
     if (sync) VO2W_CUDA_OK(cudaStreamSynchronize(st));
     return VO2W_OK;
@@ -618,29 +688,49 @@ extern "C" int vo2w_generator_forward_host_async(vo2w_generator* g, const float*
                              mel_dev, wav_dev, stream, false);
 }
 
+namespace {
+struct TapRef { size_t off = 0; int C = 0; long long L = 0; bool is_bf16_buf = false; float inv_slope = 1.0f; };
+// where the activation `tap` of the last forward lives in the workspace; false = this mode / schedule never writes it
+bool find_tap(const vo2w_generator* g, const std::string& name, TapRef& t) {
+    const Plan& p = g->last;
+    const bool bf = g->precision == VO2W_PREC_BF16;
+    if (name == "conv_pre" && !bf) {
+        t.off = p.c0_f32; t.C = g->cfg.upsample_initial_channel; t.L = p.T;
+        return true;
+    }
+    for (int i = 0; i < g->n_stage; ++i) {
+        bool found = false;
+        // "ups.i" in bf16 mode: the value recovered from the stream
+        if (name == "ups." + std::to_string(i)) { t.off = bf ? p.st[i].xa : p.st[i].x_f32; found = true; t.is_bf16_buf = bf; t.inv_slope = bf ? 10.0f : 1.0f; }
+        else if (name == "mrf." + std::to_string(i) && !bf) { t.off = p.st[i].xs; found = true; }
+        else if (name == "mrf_act." + std::to_string(i) && bf) {
+            if (i + 1 == g->n_stage && g->last_fused_post) return false;   // conv_post consumed it inside the MRF launch
+            t.off = p.st[i].mrf; found = true; t.is_bf16_buf = true;
+        }
+        if (found) { t.C = p.st[i].C; t.L = p.st[i].L; return true; }
+    }
+    return false;
+}
+}  // namespace
+
+extern "C" int vo2w_generator_has_tap(const vo2w_generator* g, const char* tap) {
+    if (!g || !tap || !g->last_ws) return 0;
+    TapRef t;
+    return find_tap(g, std::string(tap), t) ? 1 : 0;
+}
+
 extern "C" long long vo2w_generator_debug_tap(vo2w_generator* g, const char* tap, float* out_host, size_t capacity) {
     VO2W_REQUIRE(g && tap && out_host, "debug_tap: null argument");
     VO2W_REQUIRE(g->last_ws, "debug_tap: no forward has run");
     const Plan& p = g->last;
     uint8_t* ws = (uint8_t*)g->last_ws;
-    const std::string name(tap);
-    size_t off = 0;
-    int C = 0;
-    long long L = 0;
-    bool found = false;
-    const bool bf = g->precision == VO2W_PREC_BF16;
-    bool is_bf16_buf = false;
-    float inv_slope = 1.0f;       // "ups.i" in bf16 mode: the value recovered from the stream
-    if (name == "conv_pre" && !bf) {
-        off = p.c0_f32; C = g->cfg.upsample_initial_channel; L = p.T; found = true;
-    }
-    for (int i = 0; i < g->n_stage && !found; ++i) {
-        if (name == "ups." + std::to_string(i)) { off = bf ? p.st[i].xa : p.st[i].x_f32; found = true; is_bf16_buf = bf; inv_slope = bf ? 10.0f : 1.0f; }
-        else if (name == "mrf." + std::to_string(i) && !bf) { off = p.st[i].xs; found = true; }
-        else if (name == "mrf_act." + std::to_string(i) && bf) { off = p.st[i].mrf; found = true; is_bf16_buf = true; }
-        if (found) { C = p.st[i].C; L = p.st[i].L; }
-    }
-    VO2W_REQUIRE(found, "debug_tap: unknown tap '%s' for this precision mode", tap);
+    TapRef t;
+    VO2W_REQUIRE(find_tap(g, std::string(tap), t), "debug_tap: unknown tap '%s' for this precision mode / schedule", tap);
+    const size_t off = t.off;
+    const int C = t.C;
+    const long long L = t.L;
+    const bool is_bf16_buf = t.is_bf16_buf;
+    const float inv_slope = t.inv_slope;
     const size_t n = (size_t)p.B * C * L;
     VO2W_REQUIRE(n <= capacity, "debug_tap: need %zu floats, capacity %zu", n, capacity);
     VO2W_CUDA_OK(cudaDeviceSynchronize());
@@ -695,6 +785,34 @@ extern "C" int vo2w_debug_layer(int transposed, int use_umma, const float* w_hos
         return rc;
     }
     VO2W_REQUIRE(res_dev == nullptr || !transposed, "debug_layer: residual only with Conv1d");
+    if (use_umma == 2) {
+        // stream_umma_kernel (persistent CTA pairs): the kernel behind conv_pre and the upsamplers of the bf16 mode
+        VO2W_REQUIRE(res_dev == nullptr, "debug_layer: the stream kernel has no residual input");
+        SuLayer S;
+        rc = transposed ? su_pack_convT(S, w_host, bias_host, Cin, Cout, k, s) : su_pack_conv(S, w_host, bias_host, Cout, Cin, k, dil_or_stride);
+        if (rc != VO2W_OK) return rc;
+        rc = su_upload(S);
+        if (rc != VO2W_OK) return rc;
+        const long long Lp = vo2w_padded_len(L);
+        __nv_bfloat16* xin = nullptr;
+        float* of = nullptr;
+        const size_t in_b = (size_t)B * S.Cin * Lp * 2, out_b = (size_t)B * S.Cout * Lo * 4;
+        VO2W_CUDA_OK(cudaMalloc(&xin, in_b));
+        VO2W_CUDA_OK(cudaMalloc(&of, out_b));
+        VO2W_CUDA_OK(cudaMemsetAsync(xin, 0, in_b, st));
+        rc = pack_ncl_to_operand(x_dev, xin, B, Cin, L, (int)Lp, in_slope, st);
+        if (rc == VO2W_OK) rc = su_launch(S, xin, nullptr, of, 1.0f, B, L, st);
+        if (rc == VO2W_OK) rc = unchunk_f32(of, out_dev, B, S.Cout, Cout, (int)Lo, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (rc == VO2W_OK && e != cudaSuccess) {
+            vo2w_set_error("debug_layer: stream kernel failed: %s", cudaGetErrorString(e));
+            rc = VO2W_E_CUDA;
+        }
+        cudaFree(xin);
+        cudaFree(of);
+        su_free(S);
+        return rc;
+    }
     PackedLayer Lr;
     rc = transposed ? pack_convT(Lr, w_host, bias_host, Cin, Cout, k, s) : pack_conv(Lr, w_host, bias_host, Cout, Cin, k, dil_or_stride);
     if (rc != VO2W_OK) return rc;

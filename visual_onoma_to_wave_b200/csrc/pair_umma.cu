@@ -21,121 +21,9 @@
 // Accumulators: D1[NB], D2[NB] in TMEM (2*NB*C <= 512 columns); conv2 of all segments accumulates into D2.
 // e2 of a tile overlaps the MMAs of the next tile; e1 is on the critical path of its segment.
 #include "pair_umma.cuh"
+#include "umma_cg.cuh"
 
 namespace {
-
-// ---------------------------------------------------------------------------------------------------
-// PTX helpers beyond common.cuh
-// ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xFFFFFFFF;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// address of the same shared-memory location in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-// barrier that receives arrivals from the peer CTA; bounded like mbar_wait (trap, never hang)
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-    if (mbar_try_wait_cluster(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait_cluster(bar, parity)) {
-        if (clock64() - t0 > 4000000000LL) __trap();
-    }
-}
-
-template <int CG>
-__device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
-    if (CG == 1)
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                     "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc),
-                     "r"(idesc), "r"(acc) : "memory");
-    else
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                     "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc),
-                     "r"(idesc), "r"(acc) : "memory");
-}
-// all tcgen05.mma issued so far by this thread arrive on `bar` (in every CTA of the pair for CG=2) when done
-template <int CG>
-__device__ __forceinline__ void mma_commit(uint32_t bar) {
-    if (CG == 1)
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-    else
-        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-                     "h"((uint16_t)3) : "memory");
-}
-template <int CG>
-__device__ __forceinline__ void tmem_alloc_cg(uint32_t dst_smem, uint32_t ncols) {
-    if (CG == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    } else {
-        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-    }
-}
-template <int CG>
-__device__ __forceinline__ void tmem_dealloc_cg(uint32_t taddr, uint32_t ncols) {
-    if (CG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// TMEM -> registers: lane i reads TMEM lane (base + i), 32 consecutive fp32 columns
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr));
-}
-__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
-    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
-__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
-    return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
-}
-
-// leaky-relu of two packed bf16 values, slope < 1: max(v, v * slope) in bf16 (HMUL2.BF16 + HMNMX2.BF16)
-__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t v, __nv_bfloat162 slope2) {
-    const __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&v);
-    const __nv_bfloat162 r = __hmax2(a, __hmul2(a, slope2));
-    return *reinterpret_cast<const uint32_t*>(&r);
-}
-__device__ __forceinline__ void prefetch_l2(const void* p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-}
 
 // barrier slots inside the static array
 enum {
@@ -156,7 +44,8 @@ enum {
 
 struct TileCoord {
     int b;          // utterance
-    int l0;         // first output sample of the tile
+    int o0;         // first sample this tile is responsible for
+    int l0;         // first sample of the tile's rows (= o0, or o0 - 3 where conv_post rides the launch: its 3-sample halo)
     bool live;      // false: padding iteration (the pair must stay in lock step), nothing is stored
 };
 __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
@@ -165,7 +54,8 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     t.live = g < p.n_tiles;
     if (!t.live) g = p.n_tiles - 1;
     t.b = g / p.tiles_per_utt;
-    t.l0 = (g - t.b * p.tiles_per_utt) * p.V;
+    t.o0 = (g - t.b * p.tiles_per_utt) * p.Vs;
+    t.l0 = p.post ? max(t.o0 - PAIR_POST_HALO, 0) : t.o0;   // the first tile starts at sample 0: rows before it are conv_post's zero padding
     return t;
 }
 
@@ -175,22 +65,6 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
 __device__ __forceinline__ void trace(const PairP& p, int role, int unit, int slot) {
     if (p.prof && blockIdx.x == 0 && unit < PAIR_TR_UNITS && (threadIdx.x & 31) == 0)
         p.prof[(size_t)gridDim.x * 16 + ((size_t)role * PAIR_TR_UNITS + unit) * 2 + slot] = (unsigned long long)clock64();
-}
-
-// MMA with both shared-memory descriptors given as their low words (start address and LBO; the high word
-// -- SBO = 128 B, descriptor version 1 -- is the same constant for every operand of this kernel).
-template <int CG>
-__device__ __forceinline__ void mma_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t acc) {
-    if (CG == 1)
-        asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-                     "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                     "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_lo), "r"(b_lo),
-                     "r"(idesc), "r"(acc), "r"(0x4008u) : "memory");
-    else
-        asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-                     "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                     "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_lo), "r"(b_lo),
-                     "r"(idesc), "r"(acc), "r"(0x4008u) : "memory");
 }
 
 // One convolution = the bias item followed by the (tap, 64-channel block) weight items, each applied to all
@@ -275,8 +149,9 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
     }
 }
 
-template <int CG, int C>
+template <int CG, int C, bool POST>
 __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid_constant__ PairP p) {
+    static_assert(!POST || C == 32, "conv_post rides the last stage only (32 channels: one TMEM load holds a whole row)");
     constexpr int NB = C >= 256 ? 1 : (C >= 64 ? 2 : 4);     // 128-row accumulator blocks per tile (2*NB*C <= 512 TMEM columns)
     constexpr int KS = C < 64 ? 2 : 4;                       // K=16 steps per weight item (64 input channels, 32 for C=32)
     constexpr int GROUPS = C / 32;                           // 32 accumulator columns per tcgen05.ld
@@ -599,6 +474,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const float s_pos = p.scale, s_neg = p.scale * p.out_slope;
         const bool single = n_seg == 1;
         const int back = 2 * p.h2max;
+        float* const part = reinterpret_cast<float*>(smem + p.part_off);   // POST: [2][PAIR_POST_K][PAIR_POST_ROWS] partial sums
         long long c_wait = 0, c_work = 0;
         for (int it = 0; it < p.iters; ++it) {
             const TileCoord t = tile_of(p, it);
@@ -678,10 +554,31 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
                 if (!single && j + 1 < ITEMS) load_item(j + 1);  // next item's residuals fly while this one is stored
                 if (ok) {
-                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
-                    // out = bf16(leaky_relu(v * scale, out_slope)), one rounding; max(a, a * slope) for slope < 1
+                    // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
                     for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
+                }
+                if constexpr (POST) {
+                    // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
+                    // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
+                    // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory;
+                    // the taps are summed across rows after the tile's barrier.  Rows outside the utterance are
+                    // conv_post's zero padding.  x is never written to HBM.
+                    if (blk > 0 || q < 128 - back) {
+                        float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
+#pragma unroll
+                        for (int jj = 0; jj < PAIR_POST_K; ++jj) {
+                            float a = 0.f;
+                            if (ok) {
+#pragma unroll
+                                for (int c = 0; c < 32; ++c) a = fmaf(v[c], p.post_w[jj * 32 + c], a);
+                            }
+                            pr[jj * PAIR_POST_ROWS] = a;
+                        }
+                    }
+                } else if (ok) {
+                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+                    // out = bf16(...), one rounding
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
                         uint4 o;
@@ -696,6 +593,28 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             if (lane == 0) {
                 if (CG == 2) mbar_arrive_remote(d2_empty_addr + 8u * (uint32_t)nd);
                 else mbar_arrive(d2_empty_addr + 8u * (uint32_t)nd);
+            }
+            if constexpr (POST) {
+                // all 8 e2 warps have left their partial sums (the buffers alternate per tile, so one barrier per tile
+                // is enough: nobody can write this buffer again before everybody has passed the next tile's barrier)
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                const float* pb = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS);
+                const int d0 = t.o0 - t.l0;                              // 3, or 0 for the first tile of an utterance
+                for (int lr = (int)threadIdx.x; lr < p.Vs; lr += 32 * PAIR_E2_WARPS) {
+                    const int l = t.o0 + lr;
+                    if (t.live && l < p.L) {
+                        float a = p.post_b;
+#pragma unroll
+                        for (int jj = 0; jj < PAIR_POST_K; ++jj) {
+                            const int rr = d0 + lr + jj - PAIR_POST_HALO;
+                            if (rr >= 0) a += pb[jj * PAIR_POST_ROWS + rr];
+                        }
+                        const float y = tanhf(a);
+                        const size_t o = (size_t)t.b * p.L + l;
+                        if (p.wav) p.wav[o] = y;
+                        if (p.wav_i16) p.wav_i16[o] = (short)(int)(y * p.i16_scale);   // numpy astype("int16") truncates toward zero
+                    }
+                }
             }
             c_work += clock64() - c1;
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 1);
@@ -780,7 +699,7 @@ int make_group(PackedGroup& G, const PackedPair* const* pairs, int n_seg) {
 
 void free_group(PackedGroup& G) { G.n_seg = 0; }
 
-int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms) {
+int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms, bool post) {
     memset(&p, 0, sizeof(p));
     p.C = C; p.L = L; p.Lp = (int)vo2w_padded_len(L);
     p.n_seg = n_seg;
@@ -804,7 +723,10 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
         if (ks[s] > kmax) kmax = ks[s];
     }
     p.V = 128 * p.NB - 2 * p.h2max;
-    p.tiles_per_utt = vo2w_ceil_div(L, p.V);
+    VO2W_REQUIRE(!post || (C == 32 && cg == 2), "pair_plan: conv_post rides the 32-channel stage on CTA pairs only");
+    p.post = post ? 1 : 0;
+    p.Vs = post ? p.V - 2 * PAIR_POST_HALO : p.V;      // conv_post needs 3 more rows of x on either side
+    p.tiles_per_utt = vo2w_ceil_div(L, p.Vs);
     p.n_tiles = B * p.tiles_per_utt;
     p.item_bytes = (uint32_t)(C / cg) * p.KB * 2;
     for (int s = 0; s < n_seg; ++s) p.seg[s].conv_bytes_rank = (uint32_t)p.seg[s].n_items * p.item_bytes;
@@ -829,6 +751,7 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     p.t_off = off; off += (uint32_t)p.t_bufs * t_bytes;
     p.ring_off = off; off += (uint32_t)p.n_slots * p.stage_bytes;
     p.ones_off = off; off += ones_bytes;
+    if (post) { p.part_off = off; off += 2u * PAIR_POST_K * PAIR_POST_ROWS * 4u; }
     p.smem_bytes = off;
     VO2W_REQUIRE(off <= PAIR_SMEM_LIMIT, "pair_plan: %u bytes of shared memory (C=%d)", off, C);
     int grid = n_sms / cg * cg;
@@ -839,30 +762,36 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
 }
 
 typedef void (*pair_kernel_t)(const PairP);
-static pair_kernel_t pair_kernel_for(int cg, int C) {
-    if (cg == 2) return C == 256 ? pair_umma_kernel<2, 256> : (C == 128 ? pair_umma_kernel<2, 128> : (C == 64 ? pair_umma_kernel<2, 64> : pair_umma_kernel<2, 32>));
-    return C == 256 ? pair_umma_kernel<1, 256> : (C == 128 ? pair_umma_kernel<1, 128> : (C == 64 ? pair_umma_kernel<1, 64> : pair_umma_kernel<1, 32>));
+static pair_kernel_t pair_kernel_for(int cg, int C, bool post = false) {
+    if (post) return pair_umma_kernel<2, 32, true>;
+    if (cg == 2) return C == 256 ? pair_umma_kernel<2, 256, false> : (C == 128 ? pair_umma_kernel<2, 128, false> : (C == 64 ? pair_umma_kernel<2, 64, false> : pair_umma_kernel<2, 32, false>));
+    return C == 256 ? pair_umma_kernel<1, 256, false> : (C == 128 ? pair_umma_kernel<1, 128, false> : (C == 64 ? pair_umma_kernel<1, 64, false> : pair_umma_kernel<1, 32, false>));
 }
 
 int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st) {
-    static int n_sms = 0;
-    static bool attr_set = false;
-    if (!attr_set) {
-        int dev = 0;
-        VO2W_CUDA_OK(cudaGetDevice(&dev));
-        VO2W_CUDA_OK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
+    static bool attr_set[VO2W_MAX_DEV];
+    const int cur = vo2w_cur_dev();
+    const int n_sms = vo2w_sm_count();
+    if (!attr_set[cur]) {
         for (int cgi = 1; cgi <= 2; ++cgi)
             for (int c = 32; c <= 256; c *= 2)
                 VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(cgi, c), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
-        attr_set = true;
+        VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(2, 32, true), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
+        attr_set[cur] = true;
     }
-    VO2W_REQUIRE(G.n_seg >= 1 && io.out_act, "pair_launch: incomplete group or missing output");
+    const bool post = io.post_w != nullptr;
+    VO2W_REQUIRE(G.n_seg >= 1 && (post ? (io.wav || io.wav_i16) : io.out_act != nullptr), "pair_launch: incomplete group or missing output");
     const int cg = G.seg[0]->cg;
     int ks[PAIR_MAX_SEG], dils[PAIR_MAX_SEG];
     for (int s = 0; s < G.n_seg; ++s) { ks[s] = G.seg[s]->k; dils[s] = G.seg[s]->dil; }
     PairP p;
-    const int grid = pair_plan(p, G.seg[0]->C, G.n_seg, ks, dils, cg, B, L, n_sms);
+    const int grid = pair_plan(p, G.seg[0]->C, G.n_seg, ks, dils, cg, B, L, n_sms, post);
     if (grid < 0) return grid;
+    if (post) {
+        memcpy(p.post_w, io.post_w, sizeof(p.post_w));
+        p.post_b = io.post_b;
+        p.wav = io.wav; p.wav_i16 = io.wav_i16; p.i16_scale = io.i16_scale;
+    }
     for (int s = 0; s < G.n_seg; ++s) {
         VO2W_REQUIRE(io.xa[s], "pair_launch: null input of segment %d", s);
         p.seg[s].xa = io.xa[s];
@@ -881,15 +810,19 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     cfg.attrs = at;
     cfg.numAttrs = 1;
     static const bool prof_on = getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';
-    static const int dbg = getenv("VO2W_PAIR_DBG") ? atoi(getenv("VO2W_PAIR_DBG")) : 0;   // timing experiments only (results are wrong)
+#ifdef VO2W_EXPERIMENTS
+    // what-if timing switches (results are WRONG under VO2W_PAIR_DBG): only in builds made with -DVO2W_EXPERIMENTS, so a
+    // stray environment variable can never corrupt the audio of the shipped library
+    static const int dbg = getenv("VO2W_PAIR_DBG") ? atoi(getenv("VO2W_PAIR_DBG")) : 0;
     p.dbg = dbg;
     static const int pf = getenv("VO2W_PAIR_PF") ? atoi(getenv("VO2W_PAIR_PF")) : 0;
     p.pf = pf;
+#endif
     if (prof_on) {
         VO2W_CUDA_OK(cudaMalloc(&p.prof, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8));
         VO2W_CUDA_OK(cudaMemsetAsync(p.prof, 0, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8, st));
     }
-    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C), p));
+    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C, post), p));
     if (prof_on) {   // debug aid: per-role cycle accounting, averaged over the CTAs that recorded it
         std::vector<unsigned long long> h((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2);
         VO2W_CUDA_OK(cudaStreamSynchronize(st));
@@ -949,11 +882,15 @@ int unchunk_bf16(const __nv_bfloat16* x, float* out, int B, int C, int L, int Lp
     return VO2W_OK;
 }
 
-extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const float* const* b1_host,
-                               const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
-                               const int* dils, int cg, const float* const* x_dev, int B, int L, float scale,
-                               float out_slope, float* out_dev, float* act_dev, void* stream) {
-    VO2W_REQUIRE(w1_host && b1_host && w2_host && b2_host && ks && dils && x_dev && act_dev, "debug_pair: null argument");
+static int debug_pair_impl(int n_seg, const float* const* w1_host, const float* const* b1_host,
+                           const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
+                           const int* dils, int cg, const float* const* x_dev, int B, int L, float scale,
+                           float out_slope, float* out_dev, float* act_dev, const float* post_w_host, float post_b,
+                           float* wav_dev, int16_t* wav_i16_dev, float i16_scale, void* stream) {
+    const bool post = post_w_host != nullptr;
+    VO2W_REQUIRE(w1_host && b1_host && w2_host && b2_host && ks && dils && x_dev && (post ? (wav_dev || wav_i16_dev) : act_dev != nullptr),
+                 "debug_pair: null argument");
+    VO2W_REQUIRE(!post || (C == 32 && cg == 2), "debug_pair_post: conv_post rides the 32-channel CTA-pair kernel only");
     VO2W_REQUIRE(n_seg >= 1 && n_seg <= PAIR_MAX_SEG, "debug_pair: %d segments", n_seg);
     int rc = vo2w_device_check();
     if (rc != VO2W_OK) return rc;
@@ -981,15 +918,23 @@ extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const flo
         rc = pack_ncl_to_operand(x_dev[s], buf[s], B, C, L, (int)Lp, 0.1f, st);
         io.xa[s] = buf[s];
     }
+    float pw[PAIR_POST_K * 32];
     if (rc == VO2W_OK) {
         io.out_act = buf[n_seg];
         io.scale = scale;
         io.out_slope = out_slope;
+        if (post) {                                   // torch layout [1, 32, 7] -> [tap][channel]
+            for (int c = 0; c < 32; ++c)
+                for (int j = 0; j < PAIR_POST_K; ++j) pw[j * 32 + c] = post_w_host[c * PAIR_POST_K + j];
+            io.out_act = nullptr;
+            io.post_w = pw; io.post_b = post_b;
+            io.wav = wav_dev; io.wav_i16 = wav_i16_dev; io.i16_scale = i16_scale;
+        }
         rc = pair_launch(G, io, B, L, st);
     }
     // out = the value a consumer recovers from the stream (activation undone), act = the stream itself
-    if (rc == VO2W_OK && out_dev) rc = unchunk_bf16(buf[n_seg], out_dev, B, C, L, (int)Lp, st, 1.0f / out_slope);
-    if (rc == VO2W_OK) rc = unchunk_bf16(buf[n_seg], act_dev, B, C, L, (int)Lp, st);
+    if (rc == VO2W_OK && out_dev && !post) rc = unchunk_bf16(buf[n_seg], out_dev, B, C, L, (int)Lp, st, 1.0f / out_slope);
+    if (rc == VO2W_OK && !post) rc = unchunk_bf16(buf[n_seg], act_dev, B, C, L, (int)Lp, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (rc == VO2W_OK && e != cudaSuccess) {
         vo2w_set_error("debug_pair: kernel failed: %s", cudaGetErrorString(e));
@@ -999,4 +944,23 @@ extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const flo
     free_group(G);
     for (int s = 0; s < n_seg; ++s) free_pair(P[s]);
     return rc;
+}
+
+extern "C" int vo2w_debug_pair(int n_seg, const float* const* w1_host, const float* const* b1_host,
+                               const float* const* w2_host, const float* const* b2_host, int C, const int* ks,
+                               const int* dils, int cg, const float* const* x_dev, int B, int L, float scale,
+                               float out_slope, float* out_dev, float* act_dev, void* stream) {
+    VO2W_REQUIRE(act_dev, "debug_pair: null argument");
+    return debug_pair_impl(n_seg, w1_host, b1_host, w2_host, b2_host, C, ks, dils, cg, x_dev, B, L, scale, out_slope, out_dev, act_dev,
+                           nullptr, 0.f, nullptr, nullptr, 0.f, stream);
+}
+
+extern "C" int vo2w_debug_pair_post(int n_seg, const float* const* w1_host, const float* const* b1_host,
+                                    const float* const* w2_host, const float* const* b2_host, const int* ks, const int* dils,
+                                    const float* const* x_dev, int B, int L, float scale, float out_slope,
+                                    const float* post_w_host, float post_b, float* wav_dev, int16_t* wav_i16_dev,
+                                    float i16_scale, void* stream) {
+    VO2W_REQUIRE(post_w_host, "debug_pair_post: null conv_post weights");
+    return debug_pair_impl(n_seg, w1_host, b1_host, w2_host, b2_host, 32, ks, dils, 2, x_dev, B, L, scale, out_slope, nullptr, nullptr,
+                           post_w_host, post_b, wav_dev, wav_i16_dev, i16_scale, stream);
 }

@@ -26,6 +26,10 @@
 // of a unit overlaps tensor-core work instead of stalling it.  TMEM (512 columns) has the room for C <= 64.
 #define PAIR_ND(C) ((C) <= 64 ? 2 : 1)
 #define PAIR_SMEM_LIMIT (226 * 1024)      // dynamic part; 227 KB per CTA minus the static barriers
+// conv_post (Conv1d C -> 1, k = 7, padding 3; models.py:145,161-163) riding the last MRF launch
+#define PAIR_POST_K 7
+#define PAIR_POST_HALO 3
+#define PAIR_POST_ROWS 512                // rows of a tile (128 * NB at C = 32)
 
 struct PairSegP {
     const __nv_bfloat16* xa;      // the stream: bf16(leaky_relu(x, 0.1)), [B][C/8][Lp][8], zero pad rows = conv1 operand;
@@ -48,6 +52,14 @@ struct PairP {
     int32_t h2max;
     int32_t NB;                   // 128-row accumulator blocks per CTA tile
     int32_t V;                    // valid output rows per tile = 128*NB - 2*h2max
+    int32_t Vs;                   // samples a tile is responsible for (= tile stride): V, or V - 6 with conv_post on board
+    int32_t post;                 // 1: conv_post + tanh ride this launch (the 32-channel MRF launch); out_act is not written
+    uint32_t part_off;            // post: [2][PAIR_POST_K][PAIR_POST_ROWS] fp32 partial sums in shared memory
+    float post_w[PAIR_POST_K * 32];   // conv_post weights [tap][channel], fp32
+    float post_b;
+    float* wav;                   // post: fp32 waveform [B][L] (optional)
+    int16_t* wav_i16;             // post: (int16)(wav * i16_scale) [B][L] (optional; utils/model.py:83-86)
+    float i16_scale;
     int32_t tiles_per_utt, n_tiles, iters;
     float out_slope, scale;
     int32_t t_rows, xa_bufs;
@@ -82,6 +94,12 @@ struct PairIO {
     __nv_bfloat16* out_act = nullptr;
     float out_slope = 0.1f;
     float scale = 1.0f;
+    // conv_post + tanh on board (last stage, 32 channels, CTA pairs): weights [PAIR_POST_K][32] fp32 on the host
+    const float* post_w = nullptr;
+    float post_b = 0.f;
+    float* wav = nullptr;
+    int16_t* wav_i16 = nullptr;
+    float i16_scale = 0.f;
 };
 
 uint16_t f32_to_bf16_rn(float f);   // pack.cu
@@ -95,5 +113,5 @@ void free_group(PackedGroup& G);
 // columns 0/1); exposed for the CPU tests
 void pack_pair_conv_host(std::vector<uint16_t>& out, const float* w, const float* bias, int C, int k, int cg);
 // fills the geometry of a launch (no pointers); returns the grid size or a negative error
-int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms);
+int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg, int B, int L, int n_sms, bool post = false);
 int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st);

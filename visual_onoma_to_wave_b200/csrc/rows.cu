@@ -76,10 +76,11 @@ int rows_transpose_add(const float* in, const float* add, float* out, int B, int
 
 int rows_linear(const float* x, const float* w, const float* bias, long long rows, int K, int N, float* y, cudaStream_t st) {
     VO2W_REQUIRE(rows > 0 && K > 0 && N > 0 && (size_t)LIN_ROWS * K * 4 <= 160 * 1024, "linear: bad shape (rows %lld K %d N %d)", rows, K, N);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[VO2W_MAX_DEV];
+    const int cur = vo2w_cur_dev();
+    if (!attr_set[cur]) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(linear_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        attr_set = true;
+        attr_set[cur] = true;
     }
     const long long blocks = (rows + LIN_ROWS - 1) / LIN_ROWS;
     VO2W_REQUIRE(blocks <= 0x7fffffffLL, "linear: too many rows");

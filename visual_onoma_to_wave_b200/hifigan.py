@@ -200,7 +200,7 @@ class Generator(nn.Module):
         return int(math.prod(self.h.upsample_rates))
 
     def infer_host(self, mel_host: torch.Tensor, device=None, int16_scale: float | None = None,
-                   sub_batch: int | None = None):
+                   sub_batch: int | None = None, out: torch.Tensor | None = None):
         """Host mel [B,80,T] -> host wav through the C ABI's host-buffer entry points.
 
         Up to ``sub_batch`` (default ``self.host_sub_batch`` = 64) utterances: one vo2w_generator_forward_host call
@@ -208,6 +208,10 @@ class Generator(nn.Module):
         sub-batches on two alternating CUDA streams (vo2w_generator_forward_host_async), each with its own
         workspace and pinned staging, so the copies of one sub-batch overlap the kernels of the other; the result is
         a fresh host tensor.  Returns float32 [B, T*hop], or int16 when ``int16_scale`` (max_wav_value) is given.
+
+        ``out``: optional caller-owned host tensor [B, T*hop] of the result dtype, ideally pinned (a serving loop keeps
+        one per shard): every device->host copy then lands in it directly -- no staging copy, no allocation, no
+        first-touch page faults -- and it is returned.
         """
         if mel_host.is_cuda or mel_host.dtype != torch.float32 or mel_host.dim() != 3 or mel_host.shape[1] != 80:
             raise RuntimeError("infer_host expects a CPU float32 mel [B,80,T]")
@@ -217,9 +221,14 @@ class Generator(nn.Module):
         B, _, T = mel_host.shape
         mel_host = mel_host.contiguous()
         sub = int(sub_batch or self.host_sub_batch)
-        self.host_out_owned = B > sub             # False: the result aliases a pinned buffer reused by the next call
+        if out is not None:
+            odt = torch.int16 if int16_scale is not None else torch.float32
+            if out.is_cuda or out.dtype != odt or tuple(out.shape) != (B, T * self.hop) or not out.is_contiguous():
+                raise RuntimeError(f"infer_host: out must be a contiguous CPU {odt} tensor of shape {(B, T * self.hop)}")
+        # False: the result aliases a pinned buffer of the generator that the next call reuses
+        self.host_out_owned = B > sub or out is not None
         if B > sub:
-            return self._infer_host_pipelined(mel_host, device, int16_scale, sub)
+            return self._infer_host_pipelined(mel_host, device, int16_scale, sub, out)
         lib = _lib.lib()
         with torch.cuda.device(device):
             handle = self._get_handle(device)
@@ -230,7 +239,8 @@ class Generator(nn.Module):
                 odt = torch.int16 if int16_scale is not None else torch.float32
                 self._host[key] = (torch.empty(B, 80, T, device=device), torch.empty(B, T * self.hop, device=device),
                                    torch.empty(B, T * self.hop, dtype=odt).pin_memory())
-            mel_dev, wav_dev, out = self._host[key]
+            mel_dev, wav_dev, pin = self._host[key]
+            out = pin if out is None else out
             stream = torch.cuda.current_stream(device).cuda_stream
             f32_ptr = None if int16_scale is not None else out.data_ptr()
             i16_ptr = out.data_ptr() if int16_scale is not None else None
@@ -241,12 +251,14 @@ class Generator(nn.Module):
             self.last_launches = lib.vo2w_generator_last_launches(handle)
         return out
 
-    def _infer_host_pipelined(self, mel_host, device, int16_scale, sub):
+    def _infer_host_pipelined(self, mel_host, device, int16_scale, sub, out=None):
         lib = _lib.lib()
         B, _, T = mel_host.shape
         odt = torch.int16 if int16_scale is not None else torch.float32
         n_out = T * self.hop
-        out = torch.empty(B, n_out, dtype=odt)
+        direct = out is not None                  # copy device -> caller's buffer, no staging
+        if out is None:
+            out = torch.empty(B, n_out, dtype=odt)
         with torch.cuda.device(device):
             handle = self._get_handle(device)
             key = (sub, T, device.index, odt)
@@ -268,7 +280,8 @@ class Generator(nn.Module):
                 if sl["pending"] is not None:
                     a, b = sl["pending"]
                     sl["stream"].synchronize()
-                    _host_copy(out[a:b], sl["pin"][: b - a])  # host copy; the other stream's kernels keep running
+                    if not direct:
+                        _host_copy(out[a:b], sl["pin"][: b - a])  # host copy; the other stream's kernels keep running
                     sl["pending"] = None
 
             for i, a in enumerate(range(0, B, sub)):
@@ -278,8 +291,9 @@ class Generator(nn.Module):
                 fresh = sl["shape"] != (b - a, T)            # the workspace layout depends on the batch size
                 sl["shape"] = (b - a, T)
                 src = mel_host[a:b]
-                f32_ptr = None if int16_scale is not None else sl["pin"].data_ptr()
-                i16_ptr = sl["pin"].data_ptr() if int16_scale is not None else None
+                dst = out[a:b] if direct else sl["pin"]
+                f32_ptr = None if int16_scale is not None else dst.data_ptr()
+                i16_ptr = dst.data_ptr() if int16_scale is not None else None
                 _lib.check(lib.vo2w_generator_forward_host_async(handle, src.data_ptr(), b - a, T, f32_ptr, i16_ptr,
                                                                  float(int16_scale or 0.0), sl["ws"].data_ptr(), sl["ws"].numel(),
                                                                  int(fresh), sl["mel"].data_ptr(), sl["wav"].data_ptr(),
@@ -300,6 +314,13 @@ class Generator(nn.Module):
         n = _lib.lib().vo2w_generator_debug_tap(self._handle, name.encode(), buf.data_ptr(), buf.numel())
         _lib.check(int(n), "vo2w_generator_debug_tap")
         return buf[:n].clone()
+
+    def has_tap(self, name: str) -> bool:
+        """Whether the last forward left the activation `name` in the workspace (a tensor a fused launch never writes
+        to HBM -- e.g. "mrf_act.3" when conv_post rides the last MRF launch -- has no tap)."""
+        if self._handle is None:
+            return False
+        return bool(_lib.lib().vo2w_generator_has_tap(self._handle, name.encode()))
 
     def launch_times(self, x: torch.Tensor):
         """One forward with a CUDA event around every launch: ([ms per launch], [kind per launch]), kind 0 = layout
@@ -384,7 +405,8 @@ class Generator(nn.Module):
         return handle
 
     def _workspace(self, handle, B, T, device):
-        key = (B, T, device.index)
+        # one workspace per (shape, device, stream): two forwards of one shape on different streams must not share it
+        key = (B, T, device.index, torch.cuda.current_stream(device).cuda_stream)
         if key in self._ws:
             self._ws.move_to_end(key)
             return self._ws[key], False

@@ -43,11 +43,13 @@ def get_vocoder(config, device, hifigan_config_path: str = "scripts/hifigan/conf
     return vocoder
 
 
-def vocoder_infer(mels, vocoder, model_config, preprocess_config, lengths=None, Normalize=True):
+def vocoder_infer(mels, vocoder, model_config, preprocess_config, lengths=None, Normalize=True, out=None):
     """scripts/utils/model.py:73-98.  ``mels`` [B,80,T] on the vocoder's device, or on the host.
 
     Host mels go through the C ABI's host-buffer entry (H2D, kernels, D2H in one call, pinned
     staging); device mels through ``vocoder(mels)`` then ``.cpu().numpy()`` as the reference does.
+    ``out`` (beyond the reference; host mels only): a caller-owned, ideally pinned host tensor [B, T*hop] the
+    waveforms are copied into directly; the returned arrays are then views of it.
     """
     name = model_config["vocoder"]["model"]
     if name != "HiFi-GAN":
@@ -57,8 +59,8 @@ def vocoder_infer(mels, vocoder, model_config, preprocess_config, lengths=None, 
         scale = preprocess_config["preprocessing"]["audio"]["max_wav_value"]
     with torch.no_grad():
         if not mels.is_cuda:
-            out = vocoder.infer_host(mels.float(), int16_scale=scale)
-            wavs = out.numpy() if vocoder.host_out_owned else out.numpy().copy()
+            res = vocoder.infer_host(mels.float(), int16_scale=scale, out=out)
+            wavs = res.numpy() if vocoder.host_out_owned else res.numpy().copy()
         else:
             wavs = vocoder(mels).squeeze(1)
             if Normalize:
