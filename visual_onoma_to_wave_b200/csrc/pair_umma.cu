@@ -27,19 +27,24 @@ namespace {
 
 // barrier slots inside the static array
 enum {
-    BAR_XA_FULL = 0,                                  // [2]  input tile landed (complete_tx)
-    BAR_XA_EMPTY = 2,                                 // [2]  conv1 finished reading it (tcgen05.commit)
-    BAR_XA_FULL_PEER = 4,                             // [2]  leader only: peer's input tile landed
-    BAR_W_FULL = 6,                                   // [PAIR_MAX_SLOTS]
-    BAR_W_EMPTY = BAR_W_FULL + PAIR_MAX_SLOTS,
-    BAR_W_FULL_PEER = BAR_W_EMPTY + PAIR_MAX_SLOTS,   // leader only
+    // "landed" barriers of the LEADER collect two arrivals per phase: its own producer's (with the byte count) and the
+    // peer CTA's relay (the peer's tile / weights landed), so the issuer waits once per operand, not twice
+    BAR_XA_FULL = 0,                                  // [4]  input tile landed (complete_tx)
+    BAR_XA_EMPTY = 4,                                 // [4]  conv1 finished reading it (tcgen05.commit)
+    BAR_XA_FULL_PEER = 8,                             // [4]  leader only: peer's input tile landed
+    BAR_W_FULL = 12,                                  // [PAIR_W_BARS] ring slot (or, weights resident: convolution) landed
+    BAR_W_EMPTY = BAR_W_FULL + PAIR_W_BARS,
+    BAR_W_FULL_PEER = BAR_W_EMPTY + PAIR_W_BARS,      // leader only
     // the accumulators and the conv2 operand buffer exist ND times (ND = 2 where TMEM has the room, C <= 64):
     // the barriers below are indexed by the buffer, unit n uses buffer n % ND with phase (n / ND) & 1
-    BAR_D1_FULL = BAR_W_FULL_PEER + PAIR_MAX_SLOTS,   // [2] conv1 accumulators complete
+    BAR_D1_FULL = BAR_W_FULL_PEER + PAIR_W_BARS,      // [2] conv1 accumulators complete
     BAR_T_FULL = BAR_D1_FULL + 2,                     // [2][4] leader only: 64-channel block kb of the conv2 operand
     BAR_D2_FULL = BAR_T_FULL + 8,                     //        written by every e1 warp of the pair
     BAR_D2_EMPTY = BAR_D2_FULL + 2,                   // [2] leader only: every e2 warp of the pair has read D2
-    BAR_COUNT = BAR_D2_EMPTY + 2
+    // split issue (one thread per convolution, see p.split): the orderings the single issuer gets from in-order execution
+    BAR_D1_EMPTY = BAR_D2_EMPTY + 2,                  // [2] leader only: every e1 warp of the pair has read D1
+    BAR_T_EMPTY = BAR_D1_EMPTY + 2,                   // [2] conv2 has finished reading the operand buffer (tcgen05.commit)
+    BAR_COUNT = BAR_T_EMPTY + 2
 };
 
 struct TileCoord {
@@ -79,7 +84,8 @@ template <int CG, int C, int NB, int KS, int NI>
 __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int issuer, uint32_t bar0, uint32_t a_addr, uint32_t a_rows,
                                            int n_items, int dil, bool second, bool keep, uint32_t d_tmem, uint32_t ring_addr,
                                            uint32_t idesc, uint32_t ones_lo, uint32_t& wit, long long& w_wait,
-                                           int k_taps, uint32_t t_bar, uint32_t t_parity, long long& t_wait, int tr_unit = -1) {
+                                           int k_taps, uint32_t t_bar, uint32_t t_parity, long long& t_wait, int widx, uint32_t& w_seen,
+                                           int tr_unit = -1) {
     constexpr uint32_t n_loc = (uint32_t)C / CG;
     constexpr uint32_t KB = C < 64 ? C : 64;
     constexpr uint32_t item_units = n_loc * KB * 2u / 16u;                    // 16-byte units of one weight item
@@ -104,14 +110,18 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
     uint32_t a_lo = a_base;                                                   // descriptor low word of (kb, tap), block 0, step 0
     int item = 0;
     while (item < n_items) {
-        const uint32_t slot = wit & slot_mask, par = (wit >> slot_shift) & 1u;
+        // weights resident (p.resident): convolution `widx` was copied to shared memory once, at kernel start, and its
+        // barrier stays complete (phase 0) for good: no ring slot, no per-stage wait / commit / relay
+        const uint32_t slot = p.resident ? (uint32_t)widx : (wit & slot_mask), par = p.resident ? 0u : ((wit >> slot_shift) & 1u);
         long long tw = 0;
         if (prof) tw = clock64();
-        mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
-        if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL_PEER + slot), par);
+        if (!p.resident || !((w_seen >> widx) & 1u)) {   // resident weights are awaited once per convolution and kernel
+            mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL + slot), par);
+            w_seen |= 1u << widx;
+        }
         if (prof) { w_wait += clock64() - tw; if (tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0); }
-        const int cnt = min(per_stage, n_items - item);
-        uint32_t b_lo = (((ring_addr + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
+        const int cnt = p.resident ? n_items : min(per_stage, n_items - item);
+        uint32_t b_lo = (((ring_addr + (p.resident ? p.wres_off[widx] : slot * p.stage_bytes)) >> 4) & 0x3FFFu) | b_lbo_field;
         int i = 0;
         if (item == 0) {
             // item 0 is the bias: D = ones[128 x 16] . (b_hi, b_lo, 0, ...)^T initialises the accumulators
@@ -143,9 +153,11 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
             if (++tap == (uint32_t)k_taps) { tap = 0; ++kb; a_lo = a_base + kb * kb_rows; }
         }
         if (prof && tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 1);
-        mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot));     // ring slot reusable once these MMAs retire
+        if (!p.resident) {
+            mma_commit<CG>(bar0 + 8u * (BAR_W_EMPTY + slot)); // ring slot reusable once these MMAs retire
+            ++wit;
+        }
         item += cnt;
-        ++wit;
     }
 }
 
@@ -173,10 +185,15 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
     if (threadIdx.x == 0) {
         for (int i = 0; i < BAR_COUNT; ++i)
             {
-            const bool by_issuers = (i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 2) || (i >= BAR_W_EMPTY && i < BAR_W_EMPTY + PAIR_MAX_SLOTS) ||
+            const bool by_issuers = (i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 4) || (i >= BAR_W_EMPTY && i < BAR_W_EMPTY + PAIR_W_BARS) ||
                                     (i >= BAR_D1_FULL && i < BAR_D1_FULL + 2) || (i >= BAR_D2_FULL && i < BAR_D2_FULL + 2);   // one tcgen05.commit per issuer warp
-            mbar_init(bar0 + 8u * i, (i >= BAR_T_FULL && i < BAR_T_FULL + 8) ? CG * PAIR_E1_WARPS
-                                     : ((i >= BAR_D2_EMPTY && i < BAR_D2_EMPTY + 2) ? CG * PAIR_E2_WARPS : (by_issuers ? NI : 1)));
+            const bool landed = (i >= BAR_XA_FULL && i < BAR_XA_FULL + 4) || (i >= BAR_W_FULL && i < BAR_W_FULL + PAIR_W_BARS);
+            uint32_t cnt = 1;
+            if ((i >= BAR_T_FULL && i < BAR_T_FULL + 8) || (i >= BAR_D1_EMPTY && i < BAR_D1_EMPTY + 2)) cnt = CG * PAIR_E1_WARPS;
+            else if (i >= BAR_D2_EMPTY && i < BAR_D2_EMPTY + 2) cnt = CG * PAIR_E2_WARPS;
+            else if (by_issuers) cnt = p.split ? 1 : NI;
+            else if (landed && CG == 2 && rank == 0) cnt = 2;
+            mbar_init(bar0 + 8u * i, cnt);
         }
         fence_mbar_init();
     }
@@ -215,7 +232,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 const TileCoord t = tile_of(p, it);
                 for (int s = 0; s < n_seg; ++s, ++n) {
                     const PairSegP& sg = p.seg[s];
-                    const int buf = n & (p.xa_bufs - 1), use = n >> (p.xa_bufs - 1);
+                    const int use = n / p.xa_bufs, buf = n - use * p.xa_bufs;
                     if (p.pf) prefetch_unit(n + 2 + p.pf);
                     trace(p, 0, n, 0);
                     if (use > 0) mbar_wait(bar0 + 8u * (BAR_XA_EMPTY + buf), (uint32_t)((use - 1) & 1));
@@ -252,7 +269,17 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
             };
             int s2 = 0;
-            if (ND == 2) {
+            if (p.resident) {
+                // every convolution of the launch fits shared memory at once: one bulk copy each, for the whole kernel
+                for (int s = 0; s < n_seg; ++s)
+                    for (int conv = 0; conv < 2; ++conv) {
+                        const PairSegP& sg = p.seg[s];
+                        const uint32_t full = bar0 + 8u * (BAR_W_FULL + 2 * s + conv);
+                        mbar_arrive_expect_tx(full, sg.conv_bytes_rank);
+                        bulk_g2s(sm0 + p.ring_off + p.wres_off[2 * s + conv], (conv ? sg.w2 : sg.w1) + (size_t)rank * sg.conv_bytes_rank,
+                                 sg.conv_bytes_rank, full);
+                    }
+            } else if (ND == 2) {
                 int s1 = 0;
                 feed(0, 0, 0);
                 for (int n = 0; n < n_units; ++n) {
@@ -280,26 +307,24 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const uint32_t idesc = umma_idesc_bf16(128u * CG, (uint32_t)C);
         const uint32_t ones_lo = (((sm0 + p.ones_off) >> 4) & 0x3FFFu) | (128u << 16);   // [2 chunks][128 rows][8], LBO = 2 KB
         const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(ND * NB * C);
-        uint32_t wit = 0;
+        uint32_t wit = 0, w_seen = 0;
         long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0;
         const bool prof = p.prof != nullptr;
         const long long c_start = clock64();
-        const int xa_mask = p.xa_bufs - 1, xa_shift = p.xa_bufs - 1;     // xa_bufs is 1 or 2
+        const int xa_bufs = p.xa_bufs;                                   // 1 .. 4
         // (n, s): unit and its segment; no divisions on this path
         auto conv1 = [&](int n, int s) {
             const PairSegP& sg = p.seg[s];
-            const int buf = n & xa_mask, use = n >> xa_shift;
+            const int use = n / xa_bufs, buf = n - use * xa_bufs;
             long long c0 = 0;
             if (prof) c0 = clock64();
             if (prof && issuer == 0) trace(p, 8, n, 0);
-            mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+            mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));   // both CTAs' tiles
             if (prof && issuer == 0) trace(p, 8, n, 1);
-            if (CG == 2) mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL_PEER + buf), (uint32_t)(use & 1));
-            if (prof && issuer == 0) trace(p, 9, n, 0);
             if (prof) { c_xa += clock64() - c0; if (issuer == 0) trace(p, 1, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
-                           d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, issuer == 0 ? n : -1);
+                           d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, 2 * s, w_seen, issuer == 0 ? n : -1);
             mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));            // input tile reusable
             mma_commit<CG>(bar0 + 8u * (BAR_D1_FULL + n % ND));          // e1 may start
             if (prof && issuer == 0) trace(p, 1, n, 1);
@@ -314,12 +339,60 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
                            true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
-                           bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t);
+                           bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
             if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
             if (prof && issuer == 0) trace(p, 2, n, 1);
         };
+        // Split issue (p.split: weights resident, C <= 64): issuer warp 0 runs every conv1, issuer warp 1 every conv2,
+        // each over ALL row blocks and on its own schedule.  One thread issuing both convolutions was the bottleneck of
+        // the small-k launches: its waits (~230 cycles per mbarrier wait even when the phase is long complete) and MMA
+        // bursts are serial, 5100 cycles per k = 3 tile at C = 64 for 1660 cycles of tensor-pipe work (event trace).
+        // What in-order execution of one thread's MMAs gave for free is explicit here: D1[n % ND] is free once e1 of
+        // unit n - ND has read it (BAR_D1_EMPTY), the conv2 operand buffer once conv2 of unit n - ND has retired
+        // (BAR_T_EMPTY, awaited by e1).
+        auto conv1s = [&](int n, int s) {
+            const PairSegP& sg = p.seg[s];
+            const int use = n / xa_bufs, buf = n - use * xa_bufs;
+            long long c0 = 0;
+            if (prof) { c0 = clock64(); trace(p, 8, n, 0); }
+            mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+            if (n >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D1_EMPTY + n % ND), (uint32_t)((n / ND - 1) & 1));
+            if (prof) { c_xa += clock64() - c0; trace(p, 1, n, 0); }
+            tc_fence_after();
+            issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
+                           d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, 2 * s, w_seen, n);
+            mma_commit<CG>(bar0 + 8u * (BAR_XA_EMPTY + buf));
+            mma_commit<CG>(bar0 + 8u * (BAR_D1_FULL + n % ND));
+            if (prof) trace(p, 1, n, 1);
+        };
+        auto conv2s = [&](int n, int it, int s) {
+            const PairSegP& sg = p.seg[s];
+            long long c0 = 0;
+            if (prof) c0 = clock64();
+            if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
+            if (prof) { c_d2 += clock64() - c0; trace(p, 2, n, 0); }
+            tc_fence_after();
+            issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
+                           true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
+            mma_commit<CG>(bar0 + 8u * (BAR_T_EMPTY + n % ND));          // operand buffer reusable once these MMAs retire
+            if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
+            if (prof) trace(p, 2, n, 1);
+        };
         int it2 = 0, s2 = 0;                          // (tile, segment) of the unit conv2 works on
-        if (ND == 2) {
+        if (p.split) {
+            if (issuer == 0) {
+                for (int n = 0; n < n_units; ++n) {
+                    conv1s(n, s2);
+                    if (++s2 == n_seg) s2 = 0;
+                }
+            } else {
+                for (int n = 0; n < n_units; ++n) {
+                    conv2s(n, it2, s2);
+                    if (++s2 == n_seg) { s2 = 0; ++it2; }
+                }
+            }
+        } else if (ND == 2) {
             int s1 = 0;                               // segment of the unit conv1 works on (one unit ahead)
             conv1(0, 0);
             for (int n = 0; n < n_units; ++n) {
@@ -335,11 +408,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 if (++s2 == n_seg) { s2 = 0; ++it2; }
             }
         }
-        if (p.prof && issuer == 0) {
+        if (p.prof && (issuer == 0 || p.split)) {
             unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
-            o[0] = (unsigned long long)(clock64() - c_start);
-            o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
-            o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2;
+            if (issuer == 0) {
+                o[0] = (unsigned long long)(clock64() - c_start);
+                o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
+            }
+            if (issuer == 1 || !p.split) { o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2; }
         }
         }   // elected thread
         __syncwarp();
@@ -347,19 +422,24 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         if (lane == 0) {
             // ================= peer relay: forward "landed" events to the leader's barriers =================
             uint32_t wit = 0;
-            const int xa_mask = p.xa_bufs - 1, xa_shift = p.xa_bufs - 1;
+            const int xa_bufs = p.xa_bufs;
             const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_shift = (uint32_t)p.slots_log2;
             auto relay_xa = [&](int n) {
-                const int buf = n & xa_mask, use = n >> xa_shift;
+                const int use = n / xa_bufs, buf = n - use * xa_bufs;
                 mbar_wait(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
-                mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_XA_FULL_PEER + buf), 0));
+                mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_XA_FULL + buf), 0));
             };
+            if (p.resident)
+                for (int i = 0; i < 2 * n_seg; ++i) {
+                    mbar_wait(bar0 + 8u * (BAR_W_FULL + i), 0u);
+                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_W_FULL + i), 0));
+                }
             auto relay_w = [&](int s) {       // the ring stages of one convolution of segment s
-                const int stages = p.seg[s].n_stages;
+                const int stages = p.resident ? 0 : p.seg[s].n_stages;
                 for (int q = 0; q < stages; ++q, ++wit) {
                     const uint32_t slot = wit & slot_mask, par = (wit >> slot_shift) & 1u;
                     mbar_wait(bar0 + 8u * (BAR_W_FULL + slot), par);
-                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_W_FULL_PEER + slot), 0));
+                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (BAR_W_FULL + slot), 0));
                 }
             };
             int s2 = 0;
@@ -389,6 +469,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const int q = q4 * 32 + lane;                    // row inside a 128-row block
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t t_full_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_T_FULL, 0) : bar0 + 8u * BAR_T_FULL;
+        const uint32_t d1_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D1_EMPTY, 0) : bar0 + 8u * BAR_D1_EMPTY;
         constexpr int UNITS_PER_KB = (C < 64 ? 1 : 2) * NB;   // 32-column groups per weight channel block x row blocks
         const __nv_bfloat162 slope2 = __floats2bfloat162_rn(0.1f, 0.1f);
         const uint32_t t_row0 = sm0 + p.t_off + (uint32_t)q * 16u;
@@ -416,6 +497,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 const long long c0 = clock64();
                 const int nd = n % ND;                   // accumulator / operand buffer of this unit
                 mbar_wait(bar0 + 8u * (BAR_D1_FULL + nd), (uint32_t)((n / ND) & 1));
+                // split issue: the operand buffer of unit n - ND must have been read by its conv2 before it is rewritten
+                if (p.split && n >= ND) mbar_wait(bar0 + 8u * (BAR_T_EMPTY + nd), (uint32_t)((n / ND - 1) & 1));
                 const long long c1 = clock64();
                 c_wait += c1 - c0;
                 if (warp == PAIR_E1_WARP0) trace(p, 3, n, 0);
@@ -446,6 +529,15 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                             if (CG == 2) mbar_arrive_remote(bar);
                             else mbar_arrive(bar);
                         }
+                    }
+                }
+                if (p.split) {                      // D1[nd] has been read: conv1 of unit n + ND may overwrite it
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        const uint32_t bar = d1_empty_addr + 8u * (uint32_t)nd;
+                        if (CG == 2) mbar_arrive_remote(bar);
+                        else mbar_arrive(bar);
                     }
                 }
                 const long long c2 = clock64();
@@ -742,14 +834,43 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     const uint32_t ones_bytes = 2u * 128u * 16u;
     p.t_bufs = PAIR_ND(C);
     p.t_bytes = t_bytes;
-    const uint32_t fixed = (uint32_t)p.t_bufs * t_bytes + (uint32_t)p.n_slots * p.stage_bytes + ones_bytes;
-    p.xa_bufs = (fixed + 2 * xa_bytes <= PAIR_SMEM_LIMIT) ? 2 : 1;
+    // Weights resident: where all convolutions of the launch fit next to the tiles (every launch of the 32-channel
+    // stage, the k = 3 launches of the 64-channel stage) they are copied once per CTA instead of streaming through the
+    // ring for every tile: the ring's per-stage wait / commit / peer relay was ~1000 idle cycles per convolution, half
+    // of a k = 3 unit at C = 32.
+    uint32_t res_total = 0;
+    for (int s = 0; s < n_seg; ++s)
+        for (int conv = 0; conv < 2; ++conv) {
+            p.wres_off[2 * s + conv] = res_total;
+            res_total += (p.seg[s].conv_bytes_rank + 127u) & ~127u;
+        }
+    p.resident = res_total <= PAIR_RESIDENT_MAX ? 1 : 0;
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_PAIR_RESIDENT") && getenv("VO2W_PAIR_RESIDENT")[0] == '0') p.resident = 0;
+#endif
+    p.split = (p.resident && p.NB >= 2) ? 1 : 0;       // two issuer warps exist where NB >= 2
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_PAIR_SPLIT") && getenv("VO2W_PAIR_SPLIT")[0] == '0') p.split = 0;
+#endif
+    const uint32_t ring_bytes = p.resident ? res_total : (uint32_t)p.n_slots * p.stage_bytes;
+    const uint32_t fixed = (uint32_t)p.t_bufs * t_bytes + ring_bytes + ones_bytes;
+    // Input tiles in flight: the small-k launches are streams (a k = 3 launch moves 722 MB for 69-277 GFLOP), and what
+    // bounds a stream is the bytes each SM has in flight (HBM bandwidth x the latency of the load -> barrier -> relay ->
+    // MMA -> commit chain, ~5 us): with 2 tiles of 36 KB the 32-channel stage sat at 2.4 TB/s.  So take every buffer that fits.
+    const uint32_t part_bytes = post ? 2u * PAIR_POST_K * PAIR_POST_ROWS * 4u : 0u;
+    int max_bufs = 4;
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_PAIR_XABUFS")) max_bufs = atoi(getenv("VO2W_PAIR_XABUFS"));
+#endif
+    p.xa_bufs = 1;
+    for (int nb = 2; nb <= max_bufs; ++nb)
+        if (fixed + part_bytes + (uint32_t)nb * xa_bytes <= PAIR_SMEM_LIMIT) p.xa_bufs = nb;
     VO2W_REQUIRE(2 * p.t_bufs * p.NB * C <= 512, "pair_plan: accumulators exceed TMEM");
     uint32_t off = 0;
+    for (int i = 0; i < 4; ++i) p.xa_off[i] = 0;
     for (int i = 0; i < p.xa_bufs; ++i) { p.xa_off[i] = off; off += xa_bytes; }
-    if (p.xa_bufs == 1) p.xa_off[1] = p.xa_off[0];
     p.t_off = off; off += (uint32_t)p.t_bufs * t_bytes;
-    p.ring_off = off; off += (uint32_t)p.n_slots * p.stage_bytes;
+    p.ring_off = off; off += ring_bytes;
     p.ones_off = off; off += ones_bytes;
     if (post) { p.part_off = off; off += 2u * PAIR_POST_K * PAIR_POST_ROWS * 4u; }
     p.smem_bytes = off;

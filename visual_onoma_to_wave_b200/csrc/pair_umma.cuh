@@ -20,6 +20,8 @@
 #define PAIR_WARP_TMEM 13
 #define PAIR_WARP_MMA0 14
 #define PAIR_MAX_SLOTS 4
+#define PAIR_W_BARS 8                     // weight barriers: ring slots, or one per convolution when the weights are resident
+#define PAIR_RESIDENT_MAX (64 * 1024)     // per CTA: all convolutions of a launch, copied once (C = 32: every launch; C = 64: k = 3, 7)
 #define PAIR_MAX_SEG 3
 // Copies of the accumulators D1 / D2 (TMEM) and of the conv2 operand buffer (shared memory).  With 2 the MMA warp
 // runs a skewed schedule -- conv1 of unit n+1 is issued before conv2 of unit n -- so that the conv1 epilogue (e1)
@@ -62,13 +64,16 @@ struct PairP {
     float i16_scale;
     int32_t tiles_per_utt, n_tiles, iters;
     float out_slope, scale;
-    int32_t t_rows, xa_bufs;
+    int32_t t_rows, xa_bufs;      // input tile buffers: 1 .. 4
+    int32_t resident;             // 1: every convolution's weights stay in shared memory for the whole kernel (no ring)
+    int32_t split;                // 1: conv1 and conv2 are issued by two threads on their own schedules (needs resident)
+    uint32_t wres_off[2 * PAIR_MAX_SEG];   // resident: byte offset of (segment, conv1 / conv2) inside the weight area
     int32_t t_bufs;               // = PAIR_ND(C): copies of the conv2 operand buffer (and of D1 / D2 in TMEM)
     uint32_t t_bytes;             // bytes of one conv2 operand buffer
     int32_t KB, ksteps, kbs_log2; // input channels per item, K=16 steps per item, log2(C / KB)
     int32_t items_per_stage, n_slots, slots_log2;   // n_slots is 2 or 4
     uint32_t item_bytes, stage_bytes;
-    uint32_t xa_off[2], t_off, ring_off, ones_off;   // byte offsets into dynamic shared memory
+    uint32_t xa_off[4], t_off, ring_off, ones_off;   // byte offsets into dynamic shared memory
     uint32_t smem_bytes;
     int32_t pf;                   // units (tile x segment) the input rows are prefetched into L2 ahead of their bulk copy
     int32_t dbg;                  // VO2W_PAIR_DBG bit mask: what-if timing experiments (1: e2 without global traffic,

@@ -15,8 +15,12 @@
 //   buffer where shared memory has room);
 // * weights stream through a 4-stage mbarrier ring, every stage serving all NB row blocks of both CTAs (M = 256 NB
 //   rows per stage); where a unit's weights fit the ring (the s = 2 upsamplers) they are loaded once per CTA;
-// * accumulators are double-buffered in TMEM (2 x NB x n_cols = 512 columns): the 8 epilogue warps drain N-tile t
-//   (tcgen05.ld.x32, bias, leaky-relu, bf16 pack, 16-byte stores) under the MMAs of N-tile t + 1.
+// * accumulators are double-buffered in TMEM (2 x NB x n_cols <= 512 columns): the 8 epilogue warps drain N-tile t
+//   (tcgen05.ld.x32, bias, leaky-relu, bf16 pack) under the MMAs of N-tile t + 1;
+// * stores: an N-tile of a transposed convolution holds an even number of phases of the same channels, so a thread
+//   owns out[s q + 2j] and out[s q + 2j + 1] of a channel chunk = 32 contiguous bytes = one full sector per store
+//   (st.global.v8.b32).  Half-sector (16 B) writes from different N-tiles made L2 fetch every output sector from DRAM
+//   first: ncu showed 440 MB read / 598 MB written for ups[1]'s 90 MB in / 361 MB out.
 // Warp roles (384 threads): 0 input producer, 1 weight producer, 2 MMA issuer (leader) / barrier relay (peer), 3 TMEM
 // owner, 4-11 epilogue.
 #include "stream_umma.cuh"
@@ -27,16 +31,22 @@
 namespace {
 
 enum {
-    SB_A_FULL = 0,                          // [2] input tile landed (complete_tx)
-    SB_A_EMPTY = 2,                         // [2] every MMA of the unit has read it (tcgen05.commit, both CTAs)
-    SB_A_FULL_PEER = 4,                     // [2] leader only: the peer's tile landed
-    SB_W_FULL = 6,                          // [SU_SLOTS]
+    SB_A_FULL = 0,                          // [SU_A_BUFS] input tile landed (complete_tx)
+    SB_A_EMPTY = SB_A_FULL + SU_A_BUFS,     // every MMA of the unit has read it (tcgen05.commit, both CTAs)
+    SB_A_FULL_PEER = SB_A_EMPTY + SU_A_BUFS,   // leader only: the peer's tile landed
+    SB_W_FULL = SB_A_FULL_PEER + SU_A_BUFS, // [SU_SLOTS]
     SB_W_EMPTY = SB_W_FULL + SU_SLOTS,
     SB_W_FULL_PEER = SB_W_EMPTY + SU_SLOTS, // leader only
     SB_ACC_FULL = SB_W_FULL_PEER + SU_SLOTS,   // [2] accumulator buffer complete (commit, both CTAs)
     SB_ACC_EMPTY = SB_ACC_FULL + 2,         // [2] leader only: all epilogue warps of the pair have read the buffer
     SB_COUNT = SB_ACC_EMPTY + 2
 };
+
+// 32 bytes to one 32-byte aligned address: a full L2 sector per thread (SASS: STG.E.ENL2.256)
+__device__ __forceinline__ void st_global_v8(void* ptr, uint4 a, uint4 b) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x),
+                 "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
+}
 
 struct SuTile {
     int b, l0, ng;
@@ -77,8 +87,9 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
-    const int a_mask = p.a_bufs - 1, a_shift = p.a_bufs - 1;          // a_bufs is 1 or 2
+    const int a_bufs = p.a_bufs;                                      // 1 .. SU_A_BUFS
     const int stages_per_tile = p.n_items * p.n_kb;
+    const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_log2 = (uint32_t)p.slots_log2;   // ring of 4 or 8 weight stages
 
     if (warp == 0) {
         // ================= input tile producer =================
@@ -86,7 +97,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             int n = 0;
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
                 const SuTile t = su_tile(p, v, (int)rank);
-                const int buf = n & a_mask, use = n >> a_shift;
+                const int use = n / a_bufs, buf = n - use * a_bufs;
                 if (use > 0) mbar_wait(bar0 + 8u * (SB_A_EMPTY + buf), (uint32_t)((use - 1) & 1));
                 const int start = VO2W_PAD_ROWS + t.l0 - p.halo_l;        // first staged row inside the padded axis
                 const int rows = min(p.a_rows, p.Lp_in - start);          // the last tile of an utterance may be short
@@ -99,7 +110,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                     bulk_g2s(dst + (uint32_t)(c * p.a_rows) * 16u, src + (size_t)c * p.Lp_in * 8, row_bytes, full);
                 // the tile after this one: pull its rows into L2 now, so that its bulk copy (which has to wait for a
                 // free buffer) is an L2 hit
-                const int vn = v + n_pairs * p.a_bufs;
+                const int vn = v + n_pairs * (p.a_bufs + p.pf_extra);
                 if (vn < p.n_units) {
                     const SuTile tn = su_tile(p, vn, (int)rank);
                     const int sn = VO2W_PAD_ROWS + tn.l0 - p.halo_l;
@@ -119,7 +130,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                 for (int tt = 0; tt < p.tiles_per_group; ++tt) {
                     const uint8_t* base = wr + (size_t)(ng * p.tiles_per_group + tt) * p.tile_w_bytes;
                     for (int s = 0; s < stages_per_tile; ++s, ++wit) {
-                        const uint32_t slot = wit & (SU_SLOTS - 1), use = wit / SU_SLOTS;
+                        const uint32_t slot = wit & slot_mask, use = wit >> slot_log2;
                         if (use > 0) mbar_wait(bar0 + 8u * (SB_W_EMPTY + slot), (use - 1) & 1u);
                         const uint32_t full = bar0 + 8u * (SB_W_FULL + slot);
                         mbar_arrive_expect_tx(full, p.stage_bytes);
@@ -135,11 +146,12 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             const uint32_t idesc = umma_idesc_bf16(256u, (uint32_t)p.n_cols);
             const uint32_t n_half = (uint32_t)p.n_cols >> 1;
             const uint32_t b_lbo_field = n_half << 16;                   // LBO = n_half * 16 B between the K chunks
-            const uint32_t a_rows = (uint32_t)p.a_rows;
+            const uint32_t a_rows = (uint32_t)p.a_rows, a_step = 2u * a_rows, b_step = 2u * n_half, n_cols = (uint32_t)p.n_cols;
+            const int nb = p.NB, ksteps = p.ksteps;
             uint32_t wit = 0, acc_it = 0;
             int n = 0;
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
-                const int buf = n & a_mask, use = n >> a_shift;
+                const int use = n / a_bufs, buf = n - use * a_bufs;
                 mbar_wait(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));
                 mbar_wait_cluster(bar0 + 8u * (SB_A_FULL_PEER + buf), (uint32_t)(use & 1));
                 tc_fence_after();
@@ -160,8 +172,8 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                         for (int kb = 0; kb < p.n_kb; ++kb, ++s) {
                             uint32_t slot;
                             if (w_wait) {
-                                slot = wit & (SU_SLOTS - 1);
-                                const uint32_t par = (wit / SU_SLOTS) & 1u;
+                                slot = wit & slot_mask;
+                                const uint32_t par = (wit >> slot_log2) & 1u;
                                 mbar_wait(bar0 + 8u * (SB_W_FULL + slot), par);
                                 mbar_wait_cluster(bar0 + 8u * (SB_W_FULL_PEER + slot), par);
                                 tc_fence_after();
@@ -169,11 +181,17 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                                 slot = (uint32_t)(tt * stages_per_tile + s);     // resident: stage index == slot
                             }
                             const uint32_t b_lo = (((sm0 + p.ring_off + slot * p.stage_bytes) >> 4) & 0x3FFFu) | b_lbo_field;
-                            const uint32_t a_kb = a_base + (uint32_t)(kb * p.KB8) * a_rows + row;
-                            for (int blk = 0; blk < p.NB; ++blk)
-                                for (int ks = 0; ks < p.ksteps; ++ks)
-                                    mma_lo<2>(d_tmem + (uint32_t)(blk * p.n_cols), a_kb + (uint32_t)(2 * ks) * a_rows + (uint32_t)(blk * 128),
-                                              b_lo + (uint32_t)(2 * ks) * n_half, idesc, (i == 0 && kb == 0 && ks == 0) ? 0u : 1u);
+                            uint32_t a_blk = a_base + (uint32_t)(kb * p.KB8) * a_rows + row, d_blk = d_tmem;
+                            const uint32_t first = (i | kb) ? 1u : 0u;       // the first K step of a tile overwrites the accumulator
+                            if (!(p.dbg & 2))
+                            for (int blk = 0; blk < nb; ++blk, a_blk += 128u, d_blk += n_cols) {
+                                uint32_t a = a_blk, b = b_lo;
+                                mma_lo<2>(d_blk, a, b, idesc, first);
+                                for (int ks = 1; ks < ksteps; ++ks) {
+                                    a += a_step; b += b_step;
+                                    mma_lo<2>(d_blk, a, b, idesc, 1u);
+                                }
+                            }
                             if (w_wait) {
                                 if (!p.resident) mma_commit<2>(bar0 + 8u * (SB_W_EMPTY + slot));   // slot reusable once these retire
                                 ++wit;
@@ -192,12 +210,12 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             uint32_t wit = 0;
             int n = 0;
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
-                const int buf = n & a_mask, use = n >> a_shift;
+                const int use = n / a_bufs, buf = n - use * a_bufs;
                 mbar_wait(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));
                 mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_A_FULL_PEER + buf), 0));
                 if (p.resident && n > 0) continue;
                 for (int s = 0; s < p.tiles_per_group * stages_per_tile; ++s, ++wit) {
-                    const uint32_t slot = wit & (SU_SLOTS - 1), par = (wit / SU_SLOTS) & 1u;
+                    const uint32_t slot = wit & slot_mask, par = (wit >> slot_log2) & 1u;
                     mbar_wait(bar0 + 8u * (SB_W_FULL + slot), par);
                     mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_W_FULL_PEER + slot), 0));
                 }
@@ -210,68 +228,98 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
         const int q = q4 * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t acc_empty = mapa_u32(bar0 + 8u * SB_ACC_EMPTY, 0);
-        const int G = p.n_cols >> 5, n_it = p.NB * G;
+        const int G = p.n_cols >> 5, gpc = p.cb >> 5;                      // 32-column groups per tile / per phase of a tile
         const size_t o_step = (size_t)p.Lp_out * 8;                       // next 8-channel chunk of the stream
         const size_t f_step = (size_t)p.L_out * 4;                        // next 4-channel chunk of the fp32 probe output
+        const bool paired = p.ph_tile >= 2;                               // the thread owns two consecutive output rows
+        const int n_it = paired ? p.NB * (G >> 1) : p.NB * G;             // work items of one accumulator buffer
         uint32_t acc_it = 0;
-        auto emit = [&](const uint32_t (&r)[32], const SuTile& t, int nt, int idx) {
-            const int blk = idx / G, g = idx - blk * G;
-            const int row = t.l0 + blk * 128 + q;
-            if (!t.live || row >= p.L_in) return;
-            const int gn = nt * p.n_cols + g * 32;
-            const int ph = gn / p.Cout, co = gn - ph * p.Cout;
-            const long long orow = (long long)p.up_s * row + ph;
-            const float* bias = p.bias + gn;
-            float v[32];
+        // bias + leaky-relu + bf16: 32 columns -> 4 x 16 bytes
+        auto convert = [&](const uint32_t (&r)[32], const float* bias, uint4 (&w)[4], float (&v)[32]) {
 #pragma unroll
             for (int c = 0; c < 32; c += 4) {
                 const float4 bv = __ldg((const float4*)(bias + c));
                 v[c] = __uint_as_float(r[c]) + bv.x; v[c + 1] = __uint_as_float(r[c + 1]) + bv.y;
                 v[c + 2] = __uint_as_float(r[c + 2]) + bv.z; v[c + 3] = __uint_as_float(r[c + 3]) + bv.w;
             }
-            if (p.out_f32) {
-                float* o = p.out_f32 + (((size_t)t.b * (p.Cout >> 2) + (co >> 2)) * p.L_out + orow) * 4;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) *(float4*)(o + (size_t)c * f_step) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+            for (int h = 0; h < 4; ++h) {
+                w[h].x = pack_bf16x2(lrelu(v[8 * h + 0], p.out_slope), lrelu(v[8 * h + 1], p.out_slope));
+                w[h].y = pack_bf16x2(lrelu(v[8 * h + 2], p.out_slope), lrelu(v[8 * h + 3], p.out_slope));
+                w[h].z = pack_bf16x2(lrelu(v[8 * h + 4], p.out_slope), lrelu(v[8 * h + 5], p.out_slope));
+                w[h].w = pack_bf16x2(lrelu(v[8 * h + 6], p.out_slope), lrelu(v[8 * h + 7], p.out_slope));
             }
-            if (p.out) {
-                // HBM stream format of the bf16 mode: bf16(leaky_relu(value)) = the next layer's MMA operand
-                __nv_bfloat16* o = p.out + (((size_t)t.b * (p.Cout >> 3) + (co >> 3)) * p.Lp_out + VO2W_PAD_ROWS + orow) * 8;
+        };
+        auto store_f32 = [&](const float (&v)[32], int b, int co, long long orow) {
+            float* o = p.out_f32 + (((size_t)b * (p.Cout >> 2) + (co >> 2)) * p.L_out + orow) * 4;
 #pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                    uint4 w;
-                    w.x = pack_bf16x2(lrelu(v[8 * h + 0], p.out_slope), lrelu(v[8 * h + 1], p.out_slope));
-                    w.y = pack_bf16x2(lrelu(v[8 * h + 2], p.out_slope), lrelu(v[8 * h + 3], p.out_slope));
-                    w.z = pack_bf16x2(lrelu(v[8 * h + 4], p.out_slope), lrelu(v[8 * h + 5], p.out_slope));
-                    w.w = pack_bf16x2(lrelu(v[8 * h + 6], p.out_slope), lrelu(v[8 * h + 7], p.out_slope));
-                    *(uint4*)(o + (size_t)h * o_step) = w;
-                }
-            }
+            for (int c = 0; c < 8; ++c) *(float4*)(o + (size_t)c * f_step) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
         };
         for (int v = pair; v < p.n_units; v += n_pairs) {
             const SuTile t = su_tile(p, v, (int)rank);
             for (int tt = 0; tt < p.tiles_per_group; ++tt, ++acc_it) {
                 const int nt = t.ng * p.tiles_per_group + tt;
+                const int pg = nt / p.cblks, cblk = nt - pg * p.cblks;    // phase group and channel block of this N-tile
                 const uint32_t ab = acc_it & 1u, au = acc_it >> 1;
                 mbar_wait(bar0 + 8u * (SB_ACC_FULL + ab), au & 1u);
                 tc_fence_after();
                 const uint32_t t_acc = t_lane + ab * (uint32_t)(p.NB * p.n_cols);
                 int idx = half;
-                for (; idx + 2 < n_it; idx += 4) {                     // two items per round trip
+                while (idx < n_it) {
+                    // paired: item = (row block, phase pair jp, channel group cg): columns of phases 2 jp and 2 jp + 1
+                    // single: item = (row block, 32-column group); the second load is the next item of this warp
+                    int blk0, blk1, g0, g1;
+                    bool two = true;
+                    if (paired) {
+                        const int per_blk = G >> 1, jc = idx % per_blk, jp = jc / gpc, cg = jc - jp * gpc;
+                        blk0 = blk1 = idx / per_blk;
+                        g0 = 2 * jp * gpc + cg;
+                        g1 = g0 + gpc;
+                    } else {
+                        blk0 = idx / G; g0 = idx - blk0 * G;
+                        two = idx + 2 < n_it;
+                        blk1 = two ? (idx + 2) / G : blk0; g1 = two ? idx + 2 - blk1 * G : g0;
+                    }
                     uint32_t ra[32], rb[32];
-                    const int b0 = idx / G, g0 = idx - b0 * G, b1 = (idx + 2) / G, g1 = idx + 2 - b1 * G;
-                    tmem_ld32(t_acc + (uint32_t)(b0 * p.n_cols + g0 * 32), ra);
-                    tmem_ld32(t_acc + (uint32_t)(b1 * p.n_cols + g1 * 32), rb);
+                    tmem_ld32(t_acc + (uint32_t)(blk0 * p.n_cols + g0 * 32), ra);
+                    tmem_ld32(t_acc + (uint32_t)(blk1 * p.n_cols + g1 * 32), rb);
                     tmem_ld_wait();
-                    emit(ra, t, nt, idx);
-                    emit(rb, t, nt, idx + 2);
-                }
-                for (; idx < n_it; idx += 2) {
-                    uint32_t ra[32];
-                    const int b0 = idx / G, g0 = idx - b0 * G;
-                    tmem_ld32(t_acc + (uint32_t)(b0 * p.n_cols + g0 * 32), ra);
-                    tmem_ld_wait();
-                    emit(ra, t, nt, idx);
+                    if (t.live && !(p.dbg & 1)) {
+                        float va[32], vb[32];
+                        uint4 wa[4], wb[4];
+                        if (paired) {
+                            const int row = t.l0 + blk0 * 128 + q;
+                            if (row < p.L_in) {
+                                const int co = cblk * p.cb + (g0 % gpc) * 32;
+                                const long long orow = (long long)p.up_s * row + pg * p.ph_tile + g0 / gpc;   // phase of group g0: even
+                                convert(ra, p.bias + nt * p.n_cols + g0 * 32, wa, va);
+                                convert(rb, p.bias + nt * p.n_cols + g1 * 32, wb, vb);
+                                if (p.out_f32) { store_f32(va, t.b, co, orow); store_f32(vb, t.b, co, orow + 1); }
+                                if (p.out) {
+                                    // rows orow, orow + 1 of a chunk are 32 contiguous, 32-byte aligned bytes: one full sector
+                                    __nv_bfloat16* o = p.out + (((size_t)t.b * (p.Cout >> 3) + (co >> 3)) * p.Lp_out + VO2W_PAD_ROWS + orow) * 8;
+#pragma unroll
+                                    for (int h = 0; h < 4; ++h) st_global_v8(o + (size_t)h * o_step, wa[h], wb[h]);
+                                }
+                            }
+                        } else {
+                            for (int e = 0; e < (two ? 2 : 1); ++e) {
+                                const int blk = e ? blk1 : blk0, g = e ? g1 : g0;
+                                const int row = t.l0 + blk * 128 + q;
+                                if (row >= p.L_in) continue;
+                                const int co = cblk * p.cb + g * 32;
+                                const long long orow = (long long)p.up_s * row + pg * p.ph_tile;
+                                convert(e ? rb : ra, p.bias + nt * p.n_cols + g * 32, wa, va);
+                                if (p.out_f32) store_f32(va, t.b, co, orow);
+                                if (p.out) {
+                                    __nv_bfloat16* o = p.out + (((size_t)t.b * (p.Cout >> 3) + (co >> 3)) * p.Lp_out + VO2W_PAD_ROWS + orow) * 8;
+#pragma unroll
+                                    for (int h = 0; h < 4; ++h) *(uint4*)(o + (size_t)h * o_step) = wa[h];
+                                }
+                            }
+                        }
+                    }
+                    idx += (!paired && two) ? 4 : 2;     // single: both items of this round trip are done
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -305,7 +353,7 @@ int su_geometry(SuLayer& L, int n_total) {
     L.n_kb = L.Cin / L.KB;
     const int a_halo = L.halo_l + L.halo_r;
     auto fits = [&](int nb, int n_cols) {
-        const size_t a = (size_t)(128 * nb + a_halo) * L.Cin * 2, ring = (size_t)SU_SLOTS * (n_cols / 2) * L.KB * 2;
+        const size_t a = (size_t)(128 * nb + a_halo) * L.Cin * 2, ring = (size_t)4 * (n_cols / 2) * L.KB * 2;   // the ring has at least 4 stages
         return a + ring + 256 <= SU_SMEM_LIMIT;
     };
     if (n_total >= 256) {
@@ -319,7 +367,7 @@ int su_geometry(SuLayer& L, int n_total) {
         L.n_cols = n_total;
         L.NB = std::min(4, 512 / (2 * n_total));
         // a memory-bound layer wants the next tile in flight: leave room for two input buffers
-        while (L.NB > 1 && (size_t)2 * (128 * L.NB + a_halo) * L.Cin * 2 + (size_t)SU_SLOTS * (n_total / 2) * L.KB * 2 + 256 > SU_SMEM_LIMIT) L.NB >>= 1;
+        while (L.NB > 1 && (size_t)2 * (128 * L.NB + a_halo) * L.Cin * 2 + (size_t)4 * (n_total / 2) * L.KB * 2 + 256 > SU_SMEM_LIMIT) L.NB >>= 1;
         VO2W_REQUIRE(fits(L.NB, n_total), "stream conv: input tile does not fit shared memory (Cin %d)", L.Cin);
     }
     L.n_tiles = n_total / L.n_cols;
@@ -328,7 +376,7 @@ int su_geometry(SuLayer& L, int n_total) {
     return VO2W_OK;
 }
 
-// get(gn, ci, nt, i) -> weight of global column gn, input channel ci for item i of tile nt (0 outside the tensor)
+// get(n, ci, nt, i) -> weight of column n of tile nt, input channel ci, item i (0 outside the tensor)
 template <typename F>
 void su_fill(SuLayer& L, F get) {
     const int n_half = L.n_cols / 2, kb8 = L.KB / 8;
@@ -342,7 +390,7 @@ void su_fill(SuLayer& L, F get) {
                     for (int c = 0; c < kb8; ++c)
                         for (int n = 0; n < n_half; ++n)
                             for (int e = 0; e < 8; ++e)
-                                L.w_host[o++] = bf16_bits(get(nt * L.n_cols + rank * n_half + n, kb * L.KB + c * 8 + e, nt, i));
+                                L.w_host[o++] = bf16_bits(get(rank * n_half + n, kb * L.KB + c * 8 + e, nt, i));
 }
 
 }  // namespace
@@ -360,7 +408,11 @@ int su_pack_conv(SuLayer& L, const float* w, const float* bias, int Cout, int Ci
     int rc = su_geometry(L, L.Cout);
     if (rc != VO2W_OK) return rc;
     for (int j = 0; j < k; ++j) L.item_shift[j] = j * dil;        // staged row of x[q + (j - (k-1)/2) dil] for q = 0
-    su_fill(L, [&](int gn, int ci, int, int i) { return (gn < Cout && ci < Cin) ? w[((size_t)gn * Cin + ci) * k + i] : 0.f; });
+    L.ph_tile = 1; L.cb = L.n_cols; L.cblks = L.n_tiles;          // tile nt = output channels [nt n_cols, (nt + 1) n_cols)
+    su_fill(L, [&](int n, int ci, int nt, int i) {
+        const int co = nt * L.n_cols + n;
+        return (co < Cout && ci < Cin) ? w[((size_t)co * Cin + ci) * k + i] : 0.f;
+    });
     L.bias_host.assign((size_t)L.n_tiles * L.n_cols, 0.f);
     for (int n = 0; n < Cout; ++n) L.bias_host[n] = bias[n];
     return VO2W_OK;
@@ -381,11 +433,21 @@ int su_pack_convT(SuLayer& L, const float* w, const float* bias, int Cin, int Co
     VO2W_REQUIRE(L.halo_l >= 0 && L.halo_r >= 0 && L.halo_l <= VO2W_PAD_ROWS && L.halo_r <= VO2W_PAD_ROWS, "stream convT: halo");
     int rc = su_geometry(L, n_total);
     if (rc != VO2W_OK) return rc;
-    VO2W_REQUIRE(L.n_cols % Cout == 0 || Cout % L.n_cols == 0, "stream convT: Cout %d vs %d-column tiles", Cout, L.n_cols);
+    // Columns of a tile: (phase, channel) = ph_tile consecutive phases of cb channels, phase-major.  An even number of
+    // phases per tile lets a thread store out[s q + 2j] and out[s q + 2j + 1] of a channel chunk as one 32-byte sector.
+    if (n_total < 256) { L.ph_tile = s; L.cb = Cout; }
+    else {
+        L.ph_tile = s % 4 == 0 ? 4 : (s % 2 == 0 ? 2 : 1);
+        while (L.ph_tile > 1 && (L.n_cols / L.ph_tile < 32 || Cout % (L.n_cols / L.ph_tile))) L.ph_tile >>= 1;
+        L.cb = L.n_cols / L.ph_tile;
+    }
+    VO2W_REQUIRE(L.cb % 32 == 0 && Cout % L.cb == 0 && s % L.ph_tile == 0 && L.ph_tile * L.cb == L.n_cols,
+                 "stream convT: cannot tile %d phases x %d channels by %d columns", s, Cout, L.n_cols);
+    L.cblks = Cout / L.cb;
     int d_min[SU_MAX_TILES];
     L.n_items = 0;
     for (int nt = 0; nt < L.n_tiles; ++nt) {
-        const int ph_lo = nt * L.n_cols / Cout, ph_hi = ((nt + 1) * L.n_cols - 1) / Cout;
+        const int ph_lo = (nt / L.cblks) * L.ph_tile, ph_hi = ph_lo + L.ph_tile - 1;
         d_min[nt] = ceil_div_i(ph_lo + pad - k + 1, s);
         const int d_max = floor_div(ph_hi + pad, s);
         L.n_items = std::max(L.n_items, d_max - d_min[nt] + 1);
@@ -396,12 +458,23 @@ int su_pack_convT(SuLayer& L, const float* w, const float* bias, int Cin, int Co
         VO2W_REQUIRE(d_min[nt] + L.n_items - 1 <= d_hi, "stream convT: tile %d reads past the halo", nt);
     }
     for (int i = 0; i < L.n_items; ++i) L.item_shift[i] = i;       // halo_l + d_lo + i
-    su_fill(L, [&](int gn, int ci, int nt, int i) {
-        const int ph = gn / Cout, co = gn - ph * Cout, j = ph + pad - s * (d_min[nt] + i);
+    auto col = [&](int nt, int n, int& ph, int& co) {
+        ph = (nt / L.cblks) * L.ph_tile + n / L.cb;
+        co = (nt % L.cblks) * L.cb + n % L.cb;
+    };
+    su_fill(L, [&](int n, int ci, int nt, int i) {
+        int ph, co;
+        col(nt, n, ph, co);
+        const int j = ph + pad - s * (d_min[nt] + i);
         return (j >= 0 && j < k) ? w[((size_t)ci * Cout + co) * k + j] : 0.f;
     });
     L.bias_host.assign((size_t)n_total, 0.f);
-    for (int n = 0; n < n_total; ++n) L.bias_host[n] = bias[n % Cout];
+    for (int nt = 0; nt < L.n_tiles; ++nt)
+        for (int n = 0; n < L.n_cols; ++n) {
+            int ph, co;
+            col(nt, n, ph, co);
+            L.bias_host[(size_t)nt * L.n_cols + n] = bias[co];
+        }
     return VO2W_OK;
 }
 
@@ -426,39 +499,80 @@ int su_plan(SuP& p, const SuLayer& L, int B, int L_in, int n_sms) {
     VO2W_REQUIRE(B > 0 && L_in > 0, "stream conv: empty batch");
     p.chunks = L.Cin / 8;
     p.KB8 = L.KB / 8; p.n_kb = L.n_kb; p.ksteps = L.KB / 16;
-    p.NB = L.NB; p.halo_l = L.halo_l;
-    p.a_rows = 128 * L.NB + L.halo_l + L.halo_r;
+    p.halo_l = L.halo_l;
+    p.ph_tile = L.ph_tile; p.cb = L.cb; p.cblks = L.cblks;
+    // Row blocks per CTA tile and input buffers.  Weights streamed per unit (big layers): the packer's NB (every weight
+    // stage serves NB x 256 rows).  Weights resident (the s = 2 upsamplers: HBM-bound streams): what bounds a stream is
+    // the bytes each SM has in flight, so take the (NB, buffers) with the most bytes of input tiles in shared memory.
+    const bool can_reside = L.n_tiles * L.n_items * L.n_kb <= 4;
+    // streamed weights: a ring as deep as shared memory allows next to one input tile (4 or 8 stages): with 4 stages of
+    // 8 KB in flight per SM the L2 -> SM weight stream of ups[1] alone took 119 us (load -> barrier -> relay -> MMA ->
+    // commit is a ~1.3 us round trip per stage)
+    const uint32_t a_max = ((uint32_t)(128 * L.NB + L.halo_l + L.halo_r) * L.Cin * 2 + 127u) & ~127u;
+    p.n_slots = (!can_reside && a_max + 8u * L.stage_bytes <= SU_SMEM_LIMIT) ? 8 : 4;
+    p.slots_log2 = p.n_slots == 8 ? 3 : 2;
+    const uint32_t ring = (uint32_t)(can_reside ? L.n_tiles * L.n_items * L.n_kb : p.n_slots) * L.stage_bytes;
+    int nb_sel = L.NB, bufs_sel = 1;
+    {
+        long long best_bytes = -1;
+        for (int nb = L.NB; nb >= 1; nb >>= 1) {
+            const uint32_t ab = ((uint32_t)(128 * nb + L.halo_l + L.halo_r) * L.Cin * 2 + 127u) & ~127u;
+            if (ab + ring > SU_SMEM_LIMIT) continue;
+            // measured on B200 (s = 2 upsamplers, B = 128): 2 buffers of the packer's NB beat both 3 buffers (171 vs 139 us at
+            // 64 channels) and more, smaller tiles (NB = 1 x 5: 267 vs 147 us at 128 channels -- the per-unit barrier round
+            // trip, ~2.4 us, is what small units cannot amortise)
+            const int bufs = (int)std::min<uint32_t>(2, (SU_SMEM_LIMIT - ring) / ab);
+            const long long bytes = (long long)bufs * ab;
+            if (bytes > best_bytes) { best_bytes = bytes; nb_sel = nb; bufs_sel = bufs; }
+            break;
+        }
+    }
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_SU_NB")) { const int f = atoi(getenv("VO2W_SU_NB")); if (f >= 1 && f <= L.NB) { nb_sel = f; bufs_sel = 0; } }
+#endif
+    p.NB = nb_sel;
+    p.a_rows = 128 * p.NB + L.halo_l + L.halo_r;
     p.n_tiles = L.n_tiles; p.n_cols = L.n_cols; p.n_items = L.n_items;
     for (int i = 0; i < SU_MAX_ITEMS; ++i) p.item_shift[i] = L.item_shift[i];
     for (int i = 0; i < SU_MAX_TILES; ++i) p.tile_shift[i] = L.tile_shift[i];
     p.L_in = L_in; p.Lp_in = (int)vo2w_padded_len(L_in);
     p.L_out = L_in * L.up_s; p.Lp_out = (int)vo2w_padded_len(p.L_out);
     p.Cout = L.Cout; p.up_s = L.up_s;
-    p.m_tiles = vo2w_ceil_div(L_in, 128 * L.NB);
+    p.m_tiles = vo2w_ceil_div(L_in, 128 * p.NB);
     p.bm_tiles = B * p.m_tiles;
     p.pair_m = (p.bm_tiles + 1) / 2;
     const int n_pairs = std::max(1, n_sms / 2);
-    // N-tile groups: split the N-tiles of an M tile over several units where that balances the persistent pairs
-    // (rounds x N-tiles per unit = time); ties go to fewer groups (the input tile is staged once per unit)
+    const uint32_t a_bytes = ((uint32_t)p.a_rows * L.Cin * 2 + 127u) & ~127u;
+    p.a_bufs = bufs_sel ? bufs_sel : (int)std::min<uint32_t>(2, (SU_SMEM_LIMIT - ring) / a_bytes);
+    p.pf_extra = 1;                          // L2 prefetch runs this many units ahead of the last buffer being filled
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_SU_ABUFS")) p.a_bufs = std::max(1, std::min(p.a_bufs, atoi(getenv("VO2W_SU_ABUFS"))));
+    if (getenv("VO2W_SU_PF")) p.pf_extra = atoi(getenv("VO2W_SU_PF"));
+#endif
+    // N-tile groups: split the N-tiles of an M tile over several units where that balances the persistent pairs.
+    // Cost of a unit in tensor-pipe cycles: its N-tiles' MMAs (M = 256: n_cols / 2 cycles per K = 16 step and row block)
+    // plus, where the input tile is single-buffered, its reload (nothing overlaps it: ~32 B/clk from L2 + latency).
     int best = 1;
     long long best_cost = -1;
-    for (int ng = 1; ng <= L.n_tiles; ng <<= 1) {
+    const long long tile_clk = (long long)L.n_items * L.n_kb * (L.KB / 16) * p.NB * (L.n_cols / 2);
+    const long long reload_clk = p.a_bufs == 1 ? (long long)a_bytes / 32 + 1500 : 0;
+    for (int ng = 1; ng <= (can_reside ? 1 : L.n_tiles); ng <<= 1) {
         if (L.n_tiles % ng) continue;
         const long long rounds = ((long long)p.pair_m * ng + n_pairs - 1) / n_pairs;
-        const long long cost = rounds * (L.n_tiles / ng) * 16 + ng;        // + ng: tie-break
+        const long long cost = rounds * ((L.n_tiles / ng) * tile_clk + reload_clk) + ng;        // + ng: ties go to fewer groups
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = ng; }
     }
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_SU_NG")) { const int f = atoi(getenv("VO2W_SU_NG")); if (f >= 1 && L.n_tiles % f == 0) best = f; }
+#endif
     p.n_groups = best;
     p.tiles_per_group = L.n_tiles / best;
     p.n_units = p.pair_m * p.n_groups;
     p.stage_bytes = L.stage_bytes;
     p.tile_w_bytes = (uint32_t)(L.n_items * L.n_kb) * L.stage_bytes;
     p.rank_w_bytes = (uint32_t)L.n_tiles * p.tile_w_bytes;
-    p.resident = (p.n_groups == 1 && L.n_tiles * L.n_items * L.n_kb <= SU_SLOTS) ? 1 : 0;
-    const uint32_t a_bytes = ((uint32_t)p.a_rows * L.Cin * 2 + 127u) & ~127u, ring = (uint32_t)SU_SLOTS * L.stage_bytes;
-    p.a_bufs = (2 * a_bytes + ring <= SU_SMEM_LIMIT) ? 2 : 1;
-    p.a_off[0] = 0;
-    p.a_off[1] = p.a_bufs == 2 ? a_bytes : 0;
+    p.resident = can_reside ? 1 : 0;
+    for (int i = 0; i < SU_A_BUFS; ++i) p.a_off[i] = i < p.a_bufs ? (uint32_t)i * a_bytes : 0u;
     p.ring_off = (uint32_t)p.a_bufs * a_bytes;
     p.smem_bytes = p.ring_off + ring;
     VO2W_REQUIRE(p.smem_bytes <= SU_SMEM_LIMIT, "stream conv: %u bytes of shared memory", p.smem_bytes);
@@ -479,6 +593,11 @@ int su_launch(const SuLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out, flo
     const int grid = su_plan(p, L, B, L_in, vo2w_sm_count());
     if (grid < 0) return grid;
     p.in = in; p.w = L.w_dev; p.bias = L.bias_dev; p.out = out; p.out_f32 = out_f32; p.out_slope = out_slope;
+#ifdef VO2W_EXPERIMENTS
+    // what-if timing switches (results are WRONG): 1 = no global stores, 2 = no MMAs
+    static const int dbg = getenv("VO2W_SU_DBG") ? atoi(getenv("VO2W_SU_DBG")) : 0;
+    p.dbg = dbg;
+#endif
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(SU_THREADS);
@@ -503,7 +622,7 @@ extern "C" int vo2w_debug_stream_pack(int transposed, const float* w, const floa
     int rc = transposed ? su_pack_convT(L, w, bias, Cin, Cout, k, dil_or_stride) : su_pack_conv(L, w, bias, Cout, Cin, k, dil_or_stride);
     if (rc != VO2W_OK) return rc;
     const int32_t head[16] = {L.Cin, L.Cout, L.up_s, L.KB, L.n_kb, L.NB, L.n_cols, L.n_tiles, L.n_items, L.halo_l, L.halo_r,
-                              (int32_t)L.stage_bytes, (int32_t)L.w_host.size(), (int32_t)L.bias_host.size(), 0, 0};
+                              (int32_t)L.stage_bytes, (int32_t)L.w_host.size(), (int32_t)L.bias_host.size(), L.ph_tile, L.cb};
     memcpy(meta, head, sizeof(head));
     for (int i = 0; i < SU_MAX_ITEMS; ++i) meta[16 + i] = L.item_shift[i];
     for (int i = 0; i < SU_MAX_TILES; ++i) meta[16 + SU_MAX_ITEMS + i] = L.tile_shift[i];

@@ -11,7 +11,8 @@
 #define SU_THREADS 384
 #define SU_EPI_WARP0 4
 #define SU_EPI_WARPS 8
-#define SU_SLOTS 4                       // weight ring stages
+#define SU_SLOTS 8                       // weight ring stages (at most; 4 or 8 are used)
+#define SU_A_BUFS 6                      // input tile buffers (at most; as many as shared memory holds)
 #define SU_MAX_ITEMS 12
 #define SU_MAX_TILES 16
 #define SU_SMEM_LIMIT (226 * 1024)
@@ -27,6 +28,8 @@ struct SuLayer {
     int KB = 0, n_kb = 0;      // input channels per weight stage, stages per item
     int NB = 1;                // 128-row blocks per CTA tile
     int n_cols = 0, n_tiles = 0, n_items = 0;
+    int ph_tile = 1, cb = 0, cblks = 1;  // a tile's columns = ph_tile phases x cb channels (phase-major); cblks = Cout / cb;
+                                         // tile nt = phase group nt / cblks, channel block nt % cblks
     int halo_l = 0, halo_r = 0;
     int item_shift[SU_MAX_ITEMS] = {};   // staged-tile row of item i for output row 0 (before the tile's own shift)
     int tile_shift[SU_MAX_TILES] = {};
@@ -48,14 +51,17 @@ struct SuP {
     int32_t KB8, n_kb, ksteps; // KB / 8, stages per item, K=16 steps per stage
     int32_t NB, a_rows, halo_l;
     int32_t n_tiles, n_cols, n_groups, tiles_per_group, n_items;
+    int32_t ph_tile, cb, cblks;
     int32_t item_shift[SU_MAX_ITEMS];
     int32_t tile_shift[SU_MAX_TILES];
     int32_t L_in, Lp_in, L_out, Lp_out, Cout, up_s;
     int32_t m_tiles, bm_tiles, pair_m, n_units;
     uint32_t stage_bytes, tile_w_bytes, rank_w_bytes;
-    int32_t a_bufs;
-    uint32_t a_off[2], ring_off, smem_bytes;
+    int32_t a_bufs, pf_extra;
+    int32_t n_slots, slots_log2;   // weight ring stages in use (4 or 8)
+    uint32_t a_off[SU_A_BUFS], ring_off, smem_bytes;
     int32_t resident;          // the weights of a unit fit the ring and every unit uses the same ones: loaded once
+    int32_t dbg;               // what-if timing switches, only settable in -DVO2W_EXPERIMENTS builds (results are wrong)
 };
 
 // w [Cout,Cin,k] (nn.Conv1d, dilation dil, "same" padding dil*(k-1)/2)
