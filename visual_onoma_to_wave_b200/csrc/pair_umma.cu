@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             if ((i >= BAR_T_FULL && i < BAR_T_FULL + 8) || (i >= BAR_D1_EMPTY && i < BAR_D1_EMPTY + 2)) cnt = CG * PAIR_E1_WARPS;
             else if (i >= BAR_D2_EMPTY && i < BAR_D2_EMPTY + 2) cnt = CG * PAIR_E2_WARPS;
             else if (by_issuers) cnt = p.split ? 1 : NI;
+            if (p.rinit && i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 4) cnt += PAIR_E2_WARPS;   // + this CTA's e2 warps (they read the tile)
             else if (landed && CG == 2 && rank == 0) cnt = 2;
             mbar_init(bar0 + 8u * i, cnt);
         }
@@ -334,11 +335,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             // D2[it % ND] drained by the e2 of tile it - ND (the operand buffer is awaited per channel block inside)
             long long c0 = 0;
             if (prof) c0 = clock64();
-            if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
+            // rinit: D2 arrives INITIALISED with the residual by the e2 warps (every tile, the first ones too)
+            if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
+            else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
             if (prof) { c_d2 += clock64() - c0; if (issuer == 0) trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
-                           true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
                            bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
             if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
             if (prof && issuer == 0) trace(p, 2, n, 1);
@@ -369,11 +372,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const PairSegP& sg = p.seg[s];
             long long c0 = 0;
             if (prof) c0 = clock64();
-            if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
+            if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
+            else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
             if (prof) { c_d2 += clock64() - c0; trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
-                           true, s > 0, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
                            bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
             mma_commit<CG>(bar0 + 8u * (BAR_T_EMPTY + n % ND));          // operand buffer reusable once these MMAs retire
             if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
@@ -568,42 +572,101 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const int back = 2 * p.h2max;
         float* const part = reinterpret_cast<float*>(smem + p.part_off);   // POST: [2][PAIR_POST_K][PAIR_POST_ROWS] partial sums
         long long c_wait = 0, c_work = 0;
-        for (int it = 0; it < p.iters; ++it) {
-            const TileCoord t = tile_of(p, it);
-            const size_t e_tile = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8;   // chunk 0, block 0 row of this thread
-            uint4 R[4][4];                               // single: [item][chunk]; MRF: [segment][chunk] of the current item
-            auto item_geom = [&](int j, int& blk, int& g, int& rel, bool& ok) {
-                const int i = half + 2 * j;
-                blk = i / GROUPS;
-                g = i % GROUPS;
-                rel = blk == 0 ? 0 : blk * 128 - back;
-                ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
-            };
-            auto load_item = [&](int j) {                // MRF launch: all segments of item j
-                int blk, g, rel; bool ok;
-                item_geom(j, blk, g, rel, ok);
-                if (!ok) return;
-                const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+        // Residual rows are fetched one use ahead (EARLY: the small stages, whose e2 is the busiest role): the registers
+        // of (tile, item j) are refilled with the next tile's rows right after their last use, so the L2 round trip runs
+        // under the rest of the tile.  With the loads issued at the top of a tile e2 waited ~1000 cycles per tile for
+        // them (ncu source page: the first use of the loaded registers was the top stall of the kernel) -- e2 is never
+        // idle at the D2_FULL wait in these launches, so nothing else covered that latency.
+        constexpr bool EARLY = ITEMS <= 2;
+        uint4 R[4][4];                                   // single: [item][chunk]; MRF: [segment][chunk] of the current item
+        auto item_geom = [&](const TileCoord& t, int j, int& blk, int& g, int& rel, bool& ok) {
+            const int i = half + 2 * j;
+            blk = i / GROUPS;
+            g = i % GROUPS;
+            rel = blk == 0 ? 0 : blk * 128 - back;
+            ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
+        };
+        auto load_res = [&](const TileCoord& t, int j) {    // single: item j into R[j]; MRF: all segments of item j into R[s]
+            int blk, g, rel; bool ok;
+            item_geom(t, j, blk, g, rel, ok);
+            if (!ok) return;
+            const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+            if (single) {
+#pragma unroll
+                for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].xa + e + (size_t)h * e_step));
+            } else {
 #pragma unroll
                 for (int s = 0; s < PAIR_MAX_SEG; ++s)
                     if (s < n_seg) {
 #pragma unroll
                         for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].xa + e + (size_t)h * e_step));
                     }
-            };
-            if (single) {
+            }
+        };
+        // Residual by initialisation (p.rinit: single-segment launches).  y = x + conv2(...): instead of fetching x again
+        // from HBM after the convolutions (the re-read mostly MISSED L2 -- ncu: 23 % read hit rate, 505 MB read from DRAM
+        // for a 361 MB tensor -- and with the stores it cost 150 of the 316 us of a k = 3 launch), the e2 warps write x
+        // into D2 BEFORE conv2 accumulates onto it: x is recovered from the staged input tile in shared memory, which holds
+        // exactly the stream rows the residual needs, and goes to TMEM with tcgen05.st.  Each warp re-initialises the
+        // (row block, column group) items it has just drained, so there is no cross-warp hazard on D2; the input tile is
+        // released (XA_EMPTY) by conv1's commit plus these warps' arrivals.
+        const bool rinit = p.rinit != 0;
+        const uint32_t xa_empty_local = bar0 + 8u * BAR_XA_EMPTY;
+        auto init_d2 = [&](int u) {
+            const int use = u / p.xa_bufs, buf = u - use * p.xa_bufs, ndu = u % ND;
+            mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
+            const PairSegP& sg = p.seg[0];
+            const uint32_t xa_row0 = sm0 + p.xa_off[buf] + (uint32_t)(q + sg.h1 + sg.h2) * 16u;
 #pragma unroll
-                for (int j = 0; j < ITEMS; ++j) {
-                    int blk, g, rel; bool ok;
-                    item_geom(j, blk, g, rel, ok);
-                    if (ok) {
-                        const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+            for (int j = 0; j < ITEMS; ++j) {
+                const int i = half + 2 * j, blk = i / GROUPS, g = i % GROUPS;
+                const int rel = blk == 0 ? 0 : blk * 128 - back;
+                uint32_t r[32];
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].xa + e + (size_t)h * e_step));
+                for (int h = 0; h < 4; ++h) {
+                    const uint4 w4 = ld_shared_v4(xa_row0 + (uint32_t)(((g * 4 + h) * sg.xa_rows + rel) * 16));
+                    const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                    for (int k2 = 0; k2 < 4; ++k2) {      // x = s >= 0 ? s : 10 s, exact in fp32
+                        const float2 f = unpack_bf16x2(w[k2]);
+                        r[h * 8 + 2 * k2] = __float_as_uint(fmaf(fminf(f.x, 0.f), 9.f, f.x));
+                        r[h * 8 + 2 * k2 + 1] = __float_as_uint(fmaf(fminf(f.y, 0.f), 9.f, f.y));
                     }
                 }
+                tmem_st32(t_lane + (uint32_t)(((ND + ndu) * NB + blk) * C + g * 32), r);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(xa_empty_local + 8u * (uint32_t)buf);
+                if (CG == 2) mbar_arrive_remote(d2_empty_addr + 8u * (uint32_t)ndu);
+                else mbar_arrive(d2_empty_addr + 8u * (uint32_t)ndu);
+            }
+        };
+        if (rinit)
+            for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
+        if (EARLY && !rinit && p.iters > 0) {
+            const TileCoord t0 = tile_of(p, 0);
+            if (single) {
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) load_res(t0, j);
             } else {
-                load_item(0);
+                load_res(t0, 0);
+            }
+        }
+        for (int it = 0; it < p.iters; ++it) {
+            const TileCoord t = tile_of(p, it);
+            const bool has_next = it + 1 < p.iters;
+            const TileCoord tn = tile_of(p, has_next ? it + 1 : it);
+            const size_t e_tile = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8;   // chunk 0, block 0 row of this thread
+            if (!EARLY && !rinit) {
+                if (single) {
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) load_res(t, j);
+                } else {
+                    load_res(t, 0);
+                }
             }
             const long long c0 = clock64();
             const int nd = it % ND;
@@ -615,7 +678,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
 #pragma unroll
             for (int j = 0; j < ITEMS; ++j) {
                 int blk, g, rel; bool ok;
-                item_geom(j, blk, g, rel, ok);
+                item_geom(t, j, blk, g, rel, ok);
                 uint32_t r[32];
                 tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk) * C + g * 32), r);
                 tmem_ld_wait();
@@ -635,7 +698,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                         }
                     }
                 };
-                if (ok) {
+                if (ok && !rinit) {
                     if (single) {
                         add_res(R[j]);
                     } else {
@@ -644,7 +707,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                             if (s < n_seg) add_res(R[s]);
                     }
                 }
-                if (!single && j + 1 < ITEMS) load_item(j + 1);  // next item's residuals fly while this one is stored
+                // the registers are free again: fetch what uses them next while this item is scaled and stored
+                if (single) {
+                    if (EARLY && !rinit && has_next) load_res(tn, j);
+                } else {
+                    if (j + 1 < ITEMS) load_res(t, j + 1);
+                    else if (EARLY && has_next) load_res(tn, 0);
+                }
                 if (ok) {
                     // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
@@ -680,11 +749,16 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     }
                 }
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                if (CG == 2) mbar_arrive_remote(d2_empty_addr + 8u * (uint32_t)nd);
-                else mbar_arrive(d2_empty_addr + 8u * (uint32_t)nd);
+            if (rinit) {
+                // this warp's part of D2[nd] is drained: initialise it for tile it + ND (init_d2 signals the issuer)
+                if (it + ND < p.iters) init_d2(it + ND);
+            } else {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (CG == 2) mbar_arrive_remote(d2_empty_addr + 8u * (uint32_t)nd);
+                    else mbar_arrive(d2_empty_addr + 8u * (uint32_t)nd);
+                }
             }
             if constexpr (POST) {
                 // all 8 e2 warps have left their partial sums (the buffers alternate per tile, so one barrier per tile
@@ -849,6 +923,10 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     if (getenv("VO2W_PAIR_RESIDENT") && getenv("VO2W_PAIR_RESIDENT")[0] == '0') p.resident = 0;
 #endif
     p.split = (p.resident && p.NB >= 2) ? 1 : 0;       // two issuer warps exist where NB >= 2
+    p.rinit = n_seg == 1 ? 1 : 0;                      // residual by initialisation of D2 (single-segment launches)
+#ifdef VO2W_EXPERIMENTS
+    if (getenv("VO2W_PAIR_RINIT") && getenv("VO2W_PAIR_RINIT")[0] == '0') p.rinit = 0;
+#endif
 #ifdef VO2W_EXPERIMENTS
     if (getenv("VO2W_PAIR_SPLIT") && getenv("VO2W_PAIR_SPLIT")[0] == '0') p.split = 0;
 #endif

@@ -67,6 +67,7 @@ struct PairP {
     int32_t t_rows, xa_bufs;      // input tile buffers: 1 .. 4
     int32_t resident;             // 1: every convolution's weights stay in shared memory for the whole kernel (no ring)
     int32_t split;                // 1: conv1 and conv2 are issued by two threads on their own schedules (needs resident)
+    int32_t rinit;                // 1: the e2 warps initialise D2 with the residual (from the staged input tile) before conv2
     uint32_t wres_off[2 * PAIR_MAX_SEG];   // resident: byte offset of (segment, conv1 / conv2) inside the weight area
     int32_t t_bufs;               // = PAIR_ND(C): copies of the conv2 operand buffer (and of D1 / D2 in TMEM)
     uint32_t t_bytes;             // bytes of one conv2 operand buffer
