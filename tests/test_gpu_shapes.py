@@ -58,19 +58,21 @@ def _check_bf16_against_emulation(wav, emu, ref, what):
         sigma = float((e - r).pow(2).mean().sqrt())
         d = w - e
         assert torch.isfinite(w).all(), what
+        # measured on B200 (tools/gpu_stats.py, 16 utterances): rms 0.90 - 0.92 sigma, max 3.7 - 5.0 sigma, worst 128-sample
+        # window 1.06 - 1.19 sigma
         rms, mx = float(d.pow(2).mean().sqrt()), float(d.abs().max())
-        assert rms <= 1.2 * sigma, (what, b, rms, sigma)
+        assert rms <= 1.5 * sigma, (what, b, rms, sigma)
         assert mx <= 10.0 * sigma, (what, b, mx, sigma)
         n = d.numel() // 128 * 128
         win = d[:n].reshape(-1, 128).pow(2).mean(1).sqrt()          # every 128-sample window
-        assert float(win.max()) <= 4.0 * sigma, (what, b, float(win.max()), sigma)
+        assert float(win.max()) <= 3.0 * sigma, (what, b, float(win.max()), sigma)
         assert snr_db(r, w) >= MIN_SNR_DB_BF16, (what, b, snr_db(r, w))
         assert ac_snr_db(r, w) >= MIN_AC_SNR_DB_BF16, (what, b, ac_snr_db(r, w))
 
 
 def _check_taps(gen, taps, n_utt, names):
     """Per-stage streams of the last forward against the emulation's: every (utterance, 128-sample window) of every tap
-    within 3 % of the tap's rms (rounding flips are ~0.5 %; a wrong tile is ~100 %), which localises a bad tile."""
+    within 3 % of the tap's rms (rounding flips measure 0.06 - 0.5 % on B200; a wrong tile is ~100 %), which localises a bad tile."""
     for name in names:
         got = gen.debug_tap(name)
         exp = taps[name][:n_utt]
