@@ -716,7 +716,6 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 }
                 if (ok) {
                     // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
-#pragma unroll
                     if (s_pos == 1.0f) {            // scale = 1 (every single-iteration launch): one multiply less per element
 #pragma unroll
                         for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c], v[c] * s_neg);

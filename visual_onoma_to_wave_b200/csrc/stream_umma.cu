@@ -348,7 +348,7 @@ uint16_t bf16_bits(float f) {
 
 // geometry shared by both packers once Cin / N_total / halos are known
 int su_geometry(SuLayer& L, int n_total) {
-    L.KB = L.Cin <= 128 ? L.Cin : 64;
+    L.KB = L.Cin <= 128 ? L.Cin : 64;                 // set again below once n_cols is known
     VO2W_REQUIRE(L.Cin % L.KB == 0, "stream conv: %d input channels do not tile by %d", L.Cin, L.KB);
     L.n_kb = L.Cin / L.KB;
     const int a_halo = L.halo_l + L.halo_r;
@@ -372,6 +372,9 @@ int su_geometry(SuLayer& L, int n_total) {
     }
     L.n_tiles = n_total / L.n_cols;
     VO2W_REQUIRE(L.n_tiles <= SU_MAX_TILES, "stream conv: %d N-tiles", L.n_tiles);
+    // a weight stage costs ~570 cycles of bookkeeping in the issuer (wait, peer relay, commit): give it 128 input channels
+    // where that keeps the stage at 16 KB, so that a stage carries >= 1000 cycles of MMAs (ups[1]: 8 -> 16 MMAs per stage)
+    if (L.Cin > 128 && L.Cin % 128 == 0 && (size_t)(L.n_cols / 2) * 128 * 2 <= 16384) { L.KB = 128; L.n_kb = L.Cin / 128; }
     L.stage_bytes = (uint32_t)(L.n_cols / 2) * L.KB * 2;
     return VO2W_OK;
 }
