@@ -487,6 +487,29 @@ def test_decoder_against_oracle_ragged_batch(dev):
     assert float((got.cpu() - ref).abs().max()) <= DECODER_TOL
 
 
+@pytest.mark.gpu
+def test_decoder_long_sequences_stay_on_the_tensor_pipe(dev):
+    """L = 1500 > 1024 keys: the reference accepts it (it builds a longer sinusoid table on the fly above max_seq_len,
+    transformer/Models.py:171-188).  The attention GEMMs + the long-row softmax must agree with the oracle, ragged lengths
+    included, and with the same utterances evaluated alone."""
+    from oracle import decoder_oracle as do
+    from visual_onoma_to_wave_b200.synthetic import seeded_decoder_state_dict, decoder_config
+    kw = dict(n_layers=2)
+    sd = seeded_decoder_state_dict(7, **kw)
+    dec = v.Decoder(decoder_config(**kw))
+    dec.load_state_dict(sd)
+    dec.eval().to(dev)
+    lens = torch.tensor([1500, 1025, 700])
+    L = int(lens.max())
+    x = torch.randn(len(lens), L, 256, generator=torch.Generator().manual_seed(9))
+    mask = torch.arange(L)[None, :] >= lens[:, None]
+    ref, _ = do.decoder_forward(sd, x, mask)
+    got, _ = dec(x.to(dev), mask.to(dev))
+    assert float((got.cpu() - ref).abs().max()) <= DECODER_TOL
+    alone, _ = dec(x[2:3, :700].contiguous().to(dev), mask[2:3, :700].contiguous().to(dev))
+    assert float((alone.cpu() - ref[2:3, :700]).abs().max()) <= DECODER_TOL
+
+
 VARIANCE_CASES = {"energy": dict(is_energy=True, is_kurtosis=False), "both": dict(is_energy=True, is_kurtosis=True)}
 VARIANCE_KEYS = ["out", "e_pred", "k_pred", "log_d", "d_round", "mel_len", "mel_mask"]
 VARIANCE_TOL = 1e-4

@@ -206,6 +206,34 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S
     }
 }
 
+// Same row softmax for rows of any length (Lp > 1024: long-form inputs, which the reference accepts -- it builds its
+// sinusoid table on the fly above max_seq_len, Models.py:171-188).  Three passes over the row (max, sum, write); the
+// row (<= 16 KB at 4096 keys) stays in L1 between them.  One warp per row.
+__global__ void __launch_bounds__(256) softmax_rows_long_kernel(float* __restrict__ S, const uint8_t* __restrict__ mask, long long rows,
+                                                                int L, int Lp, int rows_per_b, float scale) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    float* row = S + (size_t)r * Lp;
+    const uint8_t* mb = mask ? mask + (size_t)(r / rows_per_b) * L : nullptr;
+    float mx = -INFINITY;
+    for (int j = lane; j < L; j += 32)
+        if (!(mb && mb[j])) mx = fmaxf(mx, row[j] * scale);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int j = lane; j < L; j += 32)
+        if (!(mb && mb[j])) sum += expf(row[j] * scale - mx);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.f / sum;
+    const bool none = mx == -INFINITY;                // an all-masked row gives NaN like the reference (and the short kernel)
+    for (int j = lane; j < Lp; j += 32) {
+        const bool dead = j >= L || (mb && mb[j]);
+        row[j] = none ? __int_as_float(0x7fc00000) : (dead ? 0.f : expf(row[j] * scale - mx) * inv);
+    }
+}
+
 }  // namespace
 
 // Attention as two batched GEMMs on the tensor pipe (conv_tf32.cu, fp32-level accuracy) around a row softmax:
@@ -217,7 +245,7 @@ int rows_attention_gemm(const float* qkv, const uint8_t* mask, float* out, int B
                         float* pv, cudaStream_t st) {
     VO2W_REQUIRE(D == n_head * AD, "attention: head size must be %d (d_model %d, heads %d)", AD, D, n_head);
     const int Lp = (L + 63) / 64 * 64;
-    VO2W_REQUIRE(Lp <= 1024, "attention: %d frames: the row softmax holds at most 1024 keys", L);
+    VO2W_REQUIRE(Lp <= 16384, "attention: %d frames", L);
     const size_t row3 = (size_t)3 * D;
     int rc = tf32_pack_strided(qkv + D, (size_t)L * row3, AD, row3, 1, B, n_head, Lp, AD, L, AD, pk, st);
     if (rc != VO2W_OK) return rc;
@@ -225,7 +253,10 @@ int rows_attention_gemm(const float* qkv, const uint8_t* mask, float* out, int B
     qk.ldx = (int)row3; qk.x_hs = AD; qk.ldo = n_head * Lp; qk.o_hs = Lp; qk.heads = n_head; qk.w_zs = (size_t)2 * Lp * AD;
     if ((rc = tf32_conv1d(qk, st)) != VO2W_OK) return rc;
     const long long rows = (long long)B * L * n_head;
-    softmax_rows_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
+    if (Lp <= 1024)      // the row fits one warp's registers: one pass
+        softmax_rows_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
+    else
+        softmax_rows_long_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
     VO2W_CUDA_OK(cudaGetLastError());
     if ((rc = tf32_pack_strided(qkv + 2 * D, (size_t)L * row3, AD, 1, row3, B, n_head, AD, Lp, AD, L, pv, st)) != VO2W_OK) return rc;
     Tf32Conv pvc{S, pv, nullptr, nullptr, out, B, L, Lp, AD, 1, 0};
@@ -395,8 +426,10 @@ extern "C" int vo2w_decoder_forward(vo2w_decoder* d, const float* x, const float
         float* dst = i + 1 == d->layers.size() ? out : cur;
         // MultiHeadAttention (SubLayers.py:31-62)
         if ((rc = conv(cur, P + l.pqkv, W + l.bqkv, nullptr, qkv, B, D, 3 * D, L, 1, 0, st)) != VO2W_OK) return rc;
-        rc = Lp > 1024 ? rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)       // longer than the row softmax holds
-                                           : rows_attention_gemm(qkv, mask, hid, B, L, D, d->n_head, att_s, att_k, att_v, st);
+        // tensor-pipe attention for every length the score tensor is sized for; the CUDA-core online-softmax kernel
+        // (no score tensor) stays for sequences beyond that
+        rc = Lp > 16384 ? rows_attention(qkv, mask, hid, B, L, D, d->n_head, st)
+                        : rows_attention_gemm(qkv, mask, hid, B, L, D, d->n_head, att_s, att_k, att_v, st);
         if (rc != VO2W_OK) return rc;
         if ((rc = conv(hid, P + l.pfc, W + l.bfc, cur, tmp, B, D, D, L, 1, 0, st)) != VO2W_OK) return rc;
         if ((rc = rows_layernorm_mask(tmp, W + l.ln1g, W + l.ln1b, mask, cur, rows, D, st)) != VO2W_OK) return rc;
