@@ -675,6 +675,34 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             c_wait += c1 - c0;
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 0);
             tc_fence_after();
+            if (rinit) {
+                // residual already inside D2: drain = activation, bf16, store.  Two TMEM loads per round trip.
+                auto store_item = [&](const uint32_t (&r)[32], int rel, int g) {
+                    float v[32];
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) v[c] = fmaxf(__uint_as_float(r[c]) * s_pos, __uint_as_float(r[c]) * s_neg);
+                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        uint4 o;
+                        o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
+                        o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
+                        *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
+                    }
+                };
+#pragma unroll
+                for (int j = 0; j < ITEMS; j += 2) {
+                    int blk0, g0, rel0, blk1, g1, rel1; bool ok0, ok1;
+                    item_geom(t, j, blk0, g0, rel0, ok0);
+                    item_geom(t, j + 1, blk1, g1, rel1, ok1);
+                    uint32_t ra[32], rb[32];
+                    tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk0) * C + g0 * 32), ra);
+                    tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk1) * C + g1 * 32), rb);
+                    tmem_ld_wait();
+                    if (ok0) store_item(ra, rel0, g0);
+                    if (ok1) store_item(rb, rel1, g1);
+                }
+            } else
 #pragma unroll
             for (int j = 0; j < ITEMS; ++j) {
                 int blk, g, rel; bool ok;
