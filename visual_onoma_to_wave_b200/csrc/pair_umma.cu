@@ -58,8 +58,14 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     TileCoord t;
     t.live = g < p.n_tiles;
     if (!t.live) g = p.n_tiles - 1;
-    t.b = g / p.tiles_per_utt;
-    t.o0 = (g - t.b * p.tiles_per_utt) * p.Vs;
+    // g / tiles_per_utt without the ~35-instruction integer division (every role calls this once or twice per tile):
+    // float estimate, exact after one correction step (g < 2^31, the estimate is off by at most 1)
+    int b = __float2int_rd(__int2float_rn(g) * p.inv_tiles_per_utt);
+    int r = g - b * p.tiles_per_utt;
+    if (r < 0) { --b; r += p.tiles_per_utt; }
+    else if (r >= p.tiles_per_utt) { ++b; r -= p.tiles_per_utt; }
+    t.b = b;
+    t.o0 = r * p.Vs;
     t.l0 = p.post ? max(t.o0 - PAIR_POST_HALO, 0) : t.o0;   // the first tile starts at sample 0: rows before it are conv_post's zero padding
     return t;
 }
@@ -927,6 +933,7 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     p.Vs = post ? p.V - 2 * PAIR_POST_HALO : p.V;      // conv_post needs 3 more rows of x on either side
     p.tiles_per_utt = vo2w_ceil_div(L, p.Vs);
     p.n_tiles = B * p.tiles_per_utt;
+    p.inv_tiles_per_utt = 1.0f / (float)p.tiles_per_utt;
     p.item_bytes = (uint32_t)(C / cg) * p.KB * 2;
     for (int s = 0; s < n_seg; ++s) p.seg[s].conv_bytes_rank = (uint32_t)p.seg[s].n_items * p.item_bytes;
     p.items_per_stage = (int)(16384u / p.item_bytes);
@@ -956,7 +963,8 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
     if (getenv("VO2W_PAIR_RESIDENT") && getenv("VO2W_PAIR_RESIDENT")[0] == '0') p.resident = 0;
 #endif
     p.split = (p.resident && p.NB >= 2) ? 1 : 0;       // two issuer warps exist where NB >= 2
-    p.rinit = n_seg == 1 ? 1 : 0;                      // residual by initialisation of D2 (single-segment launches)
+    p.rinit = (n_seg == 1 && !post) ? 1 : 0;           // residual by initialisation of D2 (single-segment launches; the
+                                                       // conv_post epilogue lives in the generic drain loop)
 #ifdef VO2W_EXPERIMENTS
     if (getenv("VO2W_PAIR_RINIT") && getenv("VO2W_PAIR_RINIT")[0] == '0') p.rinit = 0;
 #endif

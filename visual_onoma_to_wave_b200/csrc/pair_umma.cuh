@@ -63,6 +63,7 @@ struct PairP {
     int16_t* wav_i16;             // post: (int16)(wav * i16_scale) [B][L] (optional; utils/model.py:83-86)
     float i16_scale;
     int32_t tiles_per_utt, n_tiles, iters;
+    float inv_tiles_per_utt;      // 1 / tiles_per_utt (tile_of's division-free split of the tile index)
     float out_slope, scale;
     int32_t t_rows, xa_bufs;      // input tile buffers: 1 .. 4
     int32_t resident;             // 1: every convolution's weights stay in shared memory for the whole kernel (no ring)
