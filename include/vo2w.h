@@ -240,6 +240,24 @@ int vo2w_varpred_destroy(vo2w_varpred* p);
 size_t vo2w_varpred_workspace_bytes(const vo2w_varpred* p, int B, int T);
 int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8_t* mask, int B, int T, float* out,
                          void* workspace, size_t workspace_bytes, void* stream);
+/* vo2w_varpred_forward_static: vo2w_varpred_forward without a caller workspace and without any allocation.  It has no
+ * counterpart in the reference; it was added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The predictor's
+ * intermediates live in a device array built into the library (VO2W_VARPRED_STATIC_BYTES, held by every GPU that loads
+ * libvo2w.so until the process exits); the call makes no cudaMalloc / cudaFree and uses no allocating library routine.
+ * Same arguments, results (bit-identical: the same kernels run) and errors as vo2w_varpred_forward, plus:
+ *   - VO2W_E_WORKSPACE when vo2w_varpred_workspace_bytes(p, B, T) > VO2W_VARPRED_STATIC_BYTES, i.e. when
+ *     B * T * 4 * (d_in + 2 * d_filter) (each term rounded up to 256 bytes) exceeds 8 MiB -- 2730 tokens for the
+ *     reference's d_in = d_filter = 256;
+ *   - the first call on a device looks the array's address up (cudaGetSymbolAddress, with the caller's current device):
+ *     make it outside graph capture;
+ *   - every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to
+ *     start at zero: every intermediate is written in full before it is read).  Two calls that overlap on the GPU --
+ *     different streams, or different handles -- race on it: serialise them, or use vo2w_varpred_forward with one
+ *     workspace per stream. */
+#define VO2W_VARPRED_STATIC_BYTES (8u << 20)
+int vo2w_varpred_forward_static(vo2w_varpred* p, const float* x, const uint8_t* mask, int B, int T, float* out,
+                                void* stream);
 int vo2w_variance_embed(const float* x, const float* value, const float* bins, int n_edges, const float* table,
                         float mean, float stdv, float control, int denorm, float* value_out, float* out,
                         long long rows, int D, void* stream);

@@ -76,6 +76,7 @@ SYMBOLS = {
     "vo2w_varpred_workspace_bytes": (C.c_size_t, [C.c_void_p, C.c_int, C.c_int]),
     "vo2w_varpred_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_size_t, C.c_void_p]),
+    "vo2w_varpred_forward_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "vo2w_variance_embed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float,
                                       C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
     "vo2w_duration_round": (C.c_int, [C.c_void_p, C.c_float, C.c_void_p, C.c_longlong, C.c_void_p]),

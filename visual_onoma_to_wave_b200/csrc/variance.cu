@@ -10,6 +10,7 @@
 // LayerNorm kernel's load, the final projection and the mask are one small kernel.  The affine steps around the
 // bucket search use explicit round-to-nearest multiplies / adds / divides (no FMA contraction) so that a value sits on
 // the same side of a bin edge as in the reference's fp32 arithmetic.
+#include <mutex>
 #include <vector>
 
 #include "conv_simt.cuh"
@@ -195,6 +196,50 @@ extern "C" int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8
     project_mask_kernel<<<grid, 256, 0, st>>>(b, W + p->wl, W + p->bl, mask, out, F, T);
     VO2W_CUDA_OK(cudaGetLastError());
     return VO2W_OK;
+}
+
+// ---- the same forward for callers that may not allocate (no counterpart in the reference) ---------------------------
+// The predictor's three intermediates live in a file-scope device array instead of a caller workspace.  Every GPU that
+// loads the library holds VO2W_VARPRED_STATIC_BYTES of it until the process exits.  In host code `varpred_static_scratch`
+// is only the symbol's host-side stand-in: its device address is looked up once per device, with that device current.
+static __device__ __align__(256) unsigned char varpred_static_scratch[VO2W_VARPRED_STATIC_BYTES];
+
+namespace {
+std::mutex static_scratch_mu;
+void* static_scratch_ptr[VO2W_MAX_DEV] = {};
+
+int static_scratch_address(void** out) {
+    int dev = -1;
+    VO2W_CUDA_OK(cudaGetDevice(&dev));
+    VO2W_REQUIRE(dev >= 0 && dev < VO2W_MAX_DEV, "varpred_forward_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(static_scratch_mu);
+    if (!static_scratch_ptr[dev]) {
+        void* ptr = nullptr;
+        VO2W_CUDA_OK(cudaGetSymbolAddress(&ptr, varpred_static_scratch));
+        VO2W_REQUIRE(ptr != nullptr && (uintptr_t)ptr % 256 == 0, "varpred_forward_static: bad scratch address %p", ptr);
+        static_scratch_ptr[dev] = ptr;
+    }
+    *out = static_scratch_ptr[dev];
+    return VO2W_OK;
+}
+}  // namespace
+
+extern "C" int vo2w_varpred_forward_static(vo2w_varpred* p, const float* x, const uint8_t* mask, int B, int T, float* out,
+                                           void* stream) {
+    VO2W_REQUIRE(p && x && out, "varpred_forward_static: null argument");
+    VO2W_REQUIRE(B > 0 && T > 0 && B <= 65535, "varpred_forward_static: bad batch (B=%d T=%d)", B, T);
+    const size_t need = vo2w_varpred_workspace_bytes(p, B, T);
+    if (need > (size_t)VO2W_VARPRED_STATIC_BYTES) {
+        vo2w_set_error("varpred_forward_static: B=%d x T=%d needs %zu bytes of scratch, the built-in array holds %zu "
+                       "(use vo2w_varpred_forward with a caller workspace)", B, T, need, (size_t)VO2W_VARPRED_STATIC_BYTES);
+        return VO2W_E_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    const int rc = static_scratch_address(&scratch);
+    if (rc != VO2W_OK) return rc;
+    // Nothing in the scratch has to start at zero: the transposed input, both convolution outputs and both LayerNorm
+    // outputs are written in full before they are read, so the previous call's contents are simply overwritten.
+    return vo2w_varpred_forward(p, x, mask, B, T, out, scratch, (size_t)VO2W_VARPRED_STATIC_BYTES, stream);
 }
 
 extern "C" int vo2w_variance_embed(const float* x, const float* value, const float* bins, int n_edges, const float* table,
