@@ -17,7 +17,7 @@ LIB = os.environ.get("VO2W_LIB_OUT") or os.path.join(HERE, "libvo2w.so")   # VO2
 SOURCES = ["errors.cu", "lr.cu", "conv_simt.cu", "conv_tf32.cu", "conv_umma.cu", "pack.cu", "pair_umma.cu", "generator.cu",
            "rows.cu", "postnet.cu", "decoder.cu", "variance.cu", "stream_umma.cu"]
 HEADERS = ["common.cuh", "conv_simt.cuh", "conv_tf32.cuh", "conv_umma.cuh", "pack.cuh", "pair_umma.cuh", "rows.cuh",
-           "stream_umma.cuh", "../../include/vo2w.h"]
+           "stream_umma.cuh", "umma_cg.cuh", "../../include/vo2w.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

@@ -563,9 +563,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         }
     } else if (warp < PAIR_E2_WARPS) {
         // ================= e2: conv2 accumulators + residuals -> global =================
-        // Runs behind the MMAs of the next tile.  Two warps per lane quarter split the (block, 32-column group)
-        // items; residual rows (prefetched into L2 by the producer) are fetched before the accumulators are
-        // ready: all items at once for a single segment, item by item for the MRF launch.
+        // Runs behind the MMAs of the next tile.  Two warps per lane quarter split the (block, 32-column group) items.
+        // The loops over items / 16-column chunks are NOT unrolled: with every loop flat this role alone was ~13 KB of
+        // straight-line code per tile, the five roles of a CTA run different code on the same four schedulers, and the
+        // ncu source page showed a third of e2's stall samples as instruction fetch (stall_no_inst) -- in launches
+        // where e2 is the busiest role (C <= 64).  Addresses are computed per chunk instead.
         constexpr int ITEMS = NB * GROUPS / 2;           // per warp
         const int q4 = warp & 3;
         const int q = q4 * 32 + lane;
@@ -574,17 +576,14 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const uint32_t d2_empty_addr = CG == 2 ? mapa_u32(bar0 + 8u * BAR_D2_EMPTY, 0) : bar0 + 8u * BAR_D2_EMPTY;
         const size_t e_step = (size_t)p.Lp * 8;
         const float s_pos = p.scale, s_neg = p.scale * p.out_slope;
-        const bool single = n_seg == 1;
         const int back = 2 * p.h2max;
         float* const part = reinterpret_cast<float*>(smem + p.part_off);   // POST: [2][PAIR_POST_K][PAIR_POST_ROWS] partial sums
         long long c_wait = 0, c_work = 0;
-        // Residual rows are fetched one use ahead (EARLY: the small stages, whose e2 is the busiest role): the registers
-        // of (tile, item j) are refilled with the next tile's rows right after their last use, so the L2 round trip runs
-        // under the rest of the tile.  With the loads issued at the top of a tile e2 waited ~1000 cycles per tile for
-        // them (ncu source page: the first use of the loaded registers was the top stall of the kernel) -- e2 is never
-        // idle at the D2_FULL wait in these launches, so nothing else covered that latency.
-        constexpr bool EARLY = ITEMS <= 2;
-        uint4 R[4][4];                                   // single: [item][chunk]; MRF: [segment][chunk] of the current item
+        // Generic drain (MRF launches, conv_post on board): the residual rows of the segments of ONE item live in R, and
+        // are fetched one use ahead -- the registers are refilled with the next item's rows (the next tile's first item
+        // after the last) right after their last use, so the L2 round trip runs under the rest of the item.  With the loads
+        // issued at the top of a tile e2 waited ~1000 cycles per tile for them (ncu source page).
+        uint4 R[PAIR_MAX_SEG][4];                        // [segment][chunk] of the current item
         auto item_geom = [&](const TileCoord& t, int j, int& blk, int& g, int& rel, bool& ok) {
             const int i = half + 2 * j;
             blk = i / GROUPS;
@@ -592,22 +591,17 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             rel = blk == 0 ? 0 : blk * 128 - back;
             ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
         };
-        auto load_res = [&](const TileCoord& t, int j) {    // single: item j into R[j]; MRF: all segments of item j into R[s]
+        auto load_res = [&](const TileCoord& t, int j) {    // all segments of item j into R[s]
             int blk, g, rel; bool ok;
             item_geom(t, j, blk, g, rel, ok);
             if (!ok) return;
             const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
-            if (single) {
 #pragma unroll
-                for (int h = 0; h < 4; ++h) R[j][h] = __ldg((const uint4*)(p.seg[0].xa + e + (size_t)h * e_step));
-            } else {
+            for (int s = 0; s < PAIR_MAX_SEG; ++s)
+                if (s < n_seg) {
 #pragma unroll
-                for (int s = 0; s < PAIR_MAX_SEG; ++s)
-                    if (s < n_seg) {
-#pragma unroll
-                        for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].xa + e + (size_t)h * e_step));
-                    }
-            }
+                    for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].xa + e + (size_t)h * e_step));
+                }
         };
         // Residual by initialisation (p.rinit: single-segment launches).  y = x + conv2(...): instead of fetching x again
         // from HBM after the convolutions (the re-read mostly MISSED L2 -- ncu: 23 % read hit rate, 505 MB read from DRAM
@@ -616,6 +610,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // exactly the stream rows the residual needs, and goes to TMEM with tcgen05.st.  Each warp re-initialises the
         // (row block, column group) items it has just drained, so there is no cross-warp hazard on D2; the input tile is
         // released (XA_EMPTY) by conv1's commit plus these warps' arrivals.
+        // Both directions walk this warp's columns in 16-column chunks: chunk cc = half (cc & 1) of item cc >> 1.
         const bool rinit = p.rinit != 0;
         const uint32_t xa_empty_local = bar0 + 8u * BAR_XA_EMPTY;
         auto init_d2 = [&](int u) {
@@ -623,14 +618,15 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
             const PairSegP& sg = p.seg[0];
             const uint32_t xa_row0 = sm0 + p.xa_off[buf] + (uint32_t)(q + sg.h1 + sg.h2) * 16u;
-#pragma unroll
-            for (int j = 0; j < ITEMS; ++j) {
-                const int i = half + 2 * j, blk = i / GROUPS, g = i % GROUPS;
+            const uint32_t d2u = t_lane + (uint32_t)((ND + ndu) * NB * C);
+#pragma unroll 1
+            for (int cc = 0; cc < 2 * ITEMS; ++cc) {
+                const int i = half + 2 * (cc >> 1), blk = i / GROUPS, hc = (i % GROUPS) * 4 + (cc & 1) * 2;
                 const int rel = blk == 0 ? 0 : blk * 128 - back;
-                uint32_t r[32];
+                uint32_t r[16];
 #pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                    const uint4 w4 = ld_shared_v4(xa_row0 + (uint32_t)(((g * 4 + h) * sg.xa_rows + rel) * 16));
+                for (int h = 0; h < 2; ++h) {
+                    const uint4 w4 = ld_shared_v4(xa_row0 + (uint32_t)(((hc + h) * sg.xa_rows + rel) * 16));
                     const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
                     for (int k2 = 0; k2 < 4; ++k2) {      // x = s >= 0 ? s : 10 s, exact in fp32
@@ -639,7 +635,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                         r[h * 8 + 2 * k2 + 1] = __float_as_uint(fmaf(fminf(f.y, 0.f), 9.f, f.y));
                     }
                 }
-                tmem_st32(t_lane + (uint32_t)(((ND + ndu) * NB + blk) * C + g * 32), r);
+                tmem_st16(d2u + (uint32_t)(blk * C + hc * 8), r);
             }
             tmem_st_wait();
             tc_fence_before();
@@ -650,30 +646,15 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 else mbar_arrive(d2_empty_addr + 8u * (uint32_t)ndu);
             }
         };
-        if (rinit)
+        if (rinit) {
             for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
-        if (EARLY && !rinit && p.iters > 0) {
-            const TileCoord t0 = tile_of(p, 0);
-            if (single) {
-#pragma unroll
-                for (int j = 0; j < ITEMS; ++j) load_res(t0, j);
-            } else {
-                load_res(t0, 0);
-            }
+        } else if (p.iters > 0) {
+            load_res(tile_of(p, 0), 0);
         }
         for (int it = 0; it < p.iters; ++it) {
             const TileCoord t = tile_of(p, it);
             const bool has_next = it + 1 < p.iters;
-            const TileCoord tn = tile_of(p, has_next ? it + 1 : it);
             const size_t e_tile = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8;   // chunk 0, block 0 row of this thread
-            if (!EARLY && !rinit) {
-                if (single) {
-#pragma unroll
-                    for (int j = 0; j < ITEMS; ++j) load_res(t, j);
-                } else {
-                    load_res(t, 0);
-                }
-            }
             const long long c0 = clock64();
             const int nd = it % ND;
             mbar_wait(bar0 + 8u * (BAR_D2_FULL + nd), (uint32_t)((it / ND) & 1));
@@ -681,117 +662,118 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             c_wait += c1 - c0;
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 0);
             tc_fence_after();
+            const uint32_t d2n = t_lane + (uint32_t)((ND + nd) * NB * C);
             if (rinit) {
-                // residual already inside D2: drain = activation, bf16, store.  Two TMEM loads per round trip.
-                auto store_item = [&](const uint32_t (&r)[32], int rel, int g) {
-                    float v[32];
+                // residual already inside D2: drain = activation, bf16, store.  The load of chunk cc + 1 is in flight
+                // while chunk cc is converted and stored.
+                auto chunk_geom = [&](int cc, uint32_t& col, size_t& e, bool& ok) {
+                    const int i = half + 2 * (cc >> 1), blk = i / GROUPS, hc = (i % GROUPS) * 4 + (cc & 1) * 2;
+                    const int rel = blk == 0 ? 0 : blk * 128 - back;
+                    col = (uint32_t)(blk * C + hc * 8);
+                    e = e_tile + (size_t)rel * 8 + (size_t)hc * e_step;
+                    ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
+                };
+                auto store_chunk = [&](const uint32_t (&r)[16], size_t e) {
+                    float v[16];
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) v[c] = fmaxf(__uint_as_float(r[c]) * s_pos, __uint_as_float(r[c]) * s_neg);
-                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+                    for (int c = 0; c < 16; ++c) v[c] = fmaxf(__uint_as_float(r[c]) * s_pos, __uint_as_float(r[c]) * s_neg);
 #pragma unroll
-                    for (int h = 0; h < 4; ++h) {
+                    for (int h = 0; h < 2; ++h) {
                         uint4 o;
                         o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
                         o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
                         *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
                     }
                 };
-#pragma unroll
-                for (int j = 0; j < ITEMS; j += 2) {
-                    int blk0, g0, rel0, blk1, g1, rel1; bool ok0, ok1;
-                    item_geom(t, j, blk0, g0, rel0, ok0);
-                    item_geom(t, j + 1, blk1, g1, rel1, ok1);
-                    uint32_t ra[32], rb[32];
-                    tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk0) * C + g0 * 32), ra);
-                    tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk1) * C + g1 * 32), rb);
+                uint32_t ra[16], rb[16];
+                uint32_t col;
+                size_t ea, eb;
+                bool oka, okb;
+                chunk_geom(0, col, ea, oka);
+                tmem_ld16(d2n + col, ra);
+#pragma unroll 1
+                for (int cc = 0; cc < 2 * ITEMS; cc += 2) {
+                    chunk_geom(cc + 1, col, eb, okb);
                     tmem_ld_wait();
-                    if (ok0) store_item(ra, rel0, g0);
-                    if (ok1) store_item(rb, rel1, g1);
-                }
-            } else
-#pragma unroll
-            for (int j = 0; j < ITEMS; ++j) {
-                int blk, g, rel; bool ok;
-                item_geom(t, j, blk, g, rel, ok);
-                uint32_t r[32];
-                tmem_ld32(t_lane + (uint32_t)(((ND + nd) * NB + blk) * C + g * 32), r);
-                tmem_ld_wait();
-                float v[32];
-#pragma unroll
-                for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]);
-                // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
-                auto add_res = [&](const uint4 (&x)[4]) {
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) {
-                        const uint32_t w[4] = {x[h].x, x[h].y, x[h].z, x[h].w};
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float2 f = unpack_bf16x2(w[i]);
-                            v[h * 8 + 2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[h * 8 + 2 * i] + f.x);
-                            v[h * 8 + 2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[h * 8 + 2 * i + 1] + f.y);
-                        }
+                    tmem_ld16(d2n + col, rb);
+                    if (oka) store_chunk(ra, ea);
+                    tmem_ld_wait();
+                    if (cc + 2 < 2 * ITEMS) {
+                        chunk_geom(cc + 2, col, ea, oka);
+                        tmem_ld16(d2n + col, ra);
                     }
-                };
-                if (ok && !rinit) {
-                    if (single) {
-                        add_res(R[j]);
-                    } else {
+                    if (okb) store_chunk(rb, eb);
+                }
+                // this warp's part of D2[nd] is drained: initialise it for tile it + ND (init_d2 signals the issuer)
+                if (it + ND < p.iters) init_d2(it + ND);
+            } else {
+                const TileCoord tn = tile_of(p, has_next ? it + 1 : it);
+#pragma unroll 1
+                for (int j = 0; j < ITEMS; ++j) {
+                    int blk, g, rel; bool ok;
+                    item_geom(t, j, blk, g, rel, ok);
+                    uint32_t r[32];
+                    tmem_ld32(d2n + (uint32_t)(blk * C + g * 32), r);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]);
+                    // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
+                    auto add_res = [&](const uint4 (&x)[4]) {
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {
+                            const uint32_t w[4] = {x[h].x, x[h].y, x[h].z, x[h].w};
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const float2 f = unpack_bf16x2(w[i]);
+                                v[h * 8 + 2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[h * 8 + 2 * i] + f.x);
+                                v[h * 8 + 2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[h * 8 + 2 * i + 1] + f.y);
+                            }
+                        }
+                    };
+                    if (ok) {
 #pragma unroll
                         for (int s = 0; s < PAIR_MAX_SEG; ++s)
                             if (s < n_seg) add_res(R[s]);
                     }
-                }
-                // the registers are free again: fetch what uses them next while this item is scaled and stored
-                if (single) {
-                    if (EARLY && !rinit && has_next) load_res(tn, j);
-                } else {
+                    // the registers are free again: fetch what uses them next while this item is scaled and stored
                     if (j + 1 < ITEMS) load_res(t, j + 1);
-                    else if (EARLY && has_next) load_res(tn, 0);
-                }
-                if (ok) {
-                    // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
-                    if (s_pos == 1.0f) {            // scale = 1 (every single-iteration launch): one multiply less per element
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c], v[c] * s_neg);
-                    } else {
+                    else if (has_next) load_res(tn, 0);
+                    if (ok) {
+                        // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
                         for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
                     }
-                }
-                if constexpr (POST) {
-                    // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
-                    // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
-                    // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory;
-                    // the taps are summed across rows after the tile's barrier.  Rows outside the utterance are
-                    // conv_post's zero padding.  x is never written to HBM.
-                    if (blk > 0 || q < 128 - back) {
-                        float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
+                    if constexpr (POST) {
+                        // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
+                        // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
+                        // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory;
+                        // the taps are summed across rows after the tile's barrier.  Rows outside the utterance are
+                        // conv_post's zero padding.  x is never written to HBM.
+                        if (blk > 0 || q < 128 - back) {
+                            float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
 #pragma unroll
-                        for (int jj = 0; jj < PAIR_POST_K; ++jj) {
-                            float a = 0.f;
-                            if (ok) {
+                            for (int jj = 0; jj < PAIR_POST_K; ++jj) {
+                                float a = 0.f;
+                                if (ok) {
 #pragma unroll
-                                for (int c = 0; c < 32; ++c) a = fmaf(v[c], p.post_w[jj * 32 + c], a);
+                                    for (int c = 0; c < 32; ++c) a = fmaf(v[c], p.post_w[jj * 32 + c], a);
+                                }
+                                pr[jj * PAIR_POST_ROWS] = a;
                             }
-                            pr[jj * PAIR_POST_ROWS] = a;
+                        }
+                    } else if (ok) {
+                        const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+                        // out = bf16(...), one rounding
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
+                            o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
+                            *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
                         }
                     }
-                } else if (ok) {
-                    const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
-                    // out = bf16(...), one rounding
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) {
-                        uint4 o;
-                        o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
-                        o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
-                        *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
-                    }
                 }
-            }
-            if (rinit) {
-                // this warp's part of D2[nd] is drained: initialise it for tile it + ND (init_d2 signals the issuer)
-                if (it + ND < p.iters) init_d2(it + ND);
-            } else {
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
