@@ -70,12 +70,20 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     return t;
 }
 
+// Cycle accounting and event traces exist only in the experiments build (-DVO2W_EXPERIMENTS): the product kernel carries
+// no clock reads and no counters (they cost registers in roles that already spill).
+#ifdef VO2W_EXPERIMENTS
+constexpr bool PAIR_PROF = true;
+#else
+constexpr bool PAIR_PROF = false;
+#endif
+__device__ __forceinline__ long long prof_clock() { return PAIR_PROF ? clock64() : 0LL; }
 // VO2W_PAIR_PROF=1: event trace of CTA 0 (the leader of pair 0): trace[role][unit][2] timestamps (clock64)
 #define PAIR_TR_UNITS 48
 #define PAIR_TR_ROLES 10     // 0 input producer, 1 conv1 issue, 2 conv2 issue, 3 e1, 4 e2, 5 weight producer
 __device__ __forceinline__ void trace(const PairP& p, int role, int unit, int slot) {
-    if (p.prof && blockIdx.x == 0 && unit < PAIR_TR_UNITS && (threadIdx.x & 31) == 0)
-        p.prof[(size_t)gridDim.x * 16 + ((size_t)role * PAIR_TR_UNITS + unit) * 2 + slot] = (unsigned long long)clock64();
+    if (PAIR_PROF && p.prof && blockIdx.x == 0 && unit < PAIR_TR_UNITS && (threadIdx.x & 31) == 0)
+        p.prof[(size_t)gridDim.x * 16 + ((size_t)role * PAIR_TR_UNITS + unit) * 2 + slot] = (unsigned long long)prof_clock();
 }
 
 // One convolution = the bias item followed by the (tap, 64-channel block) weight items, each applied to all
@@ -120,12 +128,12 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
         // barrier stays complete (phase 0) for good: no ring slot, no per-stage wait / commit / relay
         const uint32_t slot = p.resident ? (uint32_t)widx : (wit & slot_mask), par = p.resident ? 0u : ((wit >> slot_shift) & 1u);
         long long tw = 0;
-        if (prof) tw = clock64();
+        if (prof) tw = prof_clock();
         if (!p.resident || !((w_seen >> widx) & 1u)) {   // resident weights are awaited once per convolution and kernel
             mbar_wait_cluster(bar0 + 8u * (BAR_W_FULL + slot), par);
             w_seen |= 1u << widx;
         }
-        if (prof) { w_wait += clock64() - tw; if (tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0); }
+        if (prof) { w_wait += prof_clock() - tw; if (tr_unit >= 0 && item == 0) trace(p, 6, tr_unit, 0); }
         const int cnt = p.resident ? n_items : min(per_stage, n_items - item);
         uint32_t b_lo = (((ring_addr + (p.resident ? p.wres_off[widx] : slot * p.stage_bytes)) >> 4) & 0x3FFFu) | b_lbo_field;
         int i = 0;
@@ -141,9 +149,9 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
                 // conv2 reads channel block kb of the operand buffer: wait until e1 has written it (the later
                 // blocks are still being converted while these MMAs run)
                 long long tt = 0;
-                if (prof) tt = clock64();
+                if (prof) tt = prof_clock();
                 mbar_wait_cluster(t_bar + 8u * kb, t_parity);
-                if (prof) t_wait += clock64() - tt;
+                if (prof) t_wait += prof_clock() - tt;
                 tc_fence_after();
             }
             if (!no_mma) {
@@ -316,19 +324,19 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const uint32_t d1 = tmem_base, d2 = tmem_base + (uint32_t)(ND * NB * C);
         uint32_t wit = 0, w_seen = 0;
         long long c_xa = 0, c_w = 0, c_t = 0, c_d2 = 0;
-        const bool prof = p.prof != nullptr;
-        const long long c_start = clock64();
+        const bool prof = PAIR_PROF && p.prof != nullptr;
+        const long long c_start = prof_clock();
         const int xa_bufs = p.xa_bufs;                                   // 1 .. 4
         // (n, s): unit and its segment; no divisions on this path
         auto conv1 = [&](int n, int s) {
             const PairSegP& sg = p.seg[s];
             const int use = n / xa_bufs, buf = n - use * xa_bufs;
             long long c0 = 0;
-            if (prof) c0 = clock64();
+            if (prof) c0 = prof_clock();
             if (prof && issuer == 0) trace(p, 8, n, 0);
             mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));   // both CTAs' tiles
             if (prof && issuer == 0) trace(p, 8, n, 1);
-            if (prof) { c_xa += clock64() - c0; if (issuer == 0) trace(p, 1, n, 0); }
+            if (prof) { c_xa += prof_clock() - c0; if (issuer == 0) trace(p, 1, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
                            d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, 2 * s, w_seen, issuer == 0 ? n : -1);
@@ -340,11 +348,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const PairSegP& sg = p.seg[s];
             // D2[it % ND] drained by the e2 of tile it - ND (the operand buffer is awaited per channel block inside)
             long long c0 = 0;
-            if (prof) c0 = clock64();
+            if (prof) c0 = prof_clock();
             // rinit: D2 arrives INITIALISED with the residual by the e2 warps (every tile, the first ones too)
             if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
             else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
-            if (prof) { c_d2 += clock64() - c0; if (issuer == 0) trace(p, 2, n, 0); }
+            if (prof) { c_d2 += prof_clock() - c0; if (issuer == 0) trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
                            true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
@@ -363,10 +371,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const PairSegP& sg = p.seg[s];
             const int use = n / xa_bufs, buf = n - use * xa_bufs;
             long long c0 = 0;
-            if (prof) { c0 = clock64(); trace(p, 8, n, 0); }
+            if (prof) { c0 = prof_clock(); trace(p, 8, n, 0); }
             mbar_wait_cluster(bar0 + 8u * (BAR_XA_FULL + buf), (uint32_t)(use & 1));
             if (n >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D1_EMPTY + n % ND), (uint32_t)((n / ND - 1) & 1));
-            if (prof) { c_xa += clock64() - c0; trace(p, 1, n, 0); }
+            if (prof) { c_xa += prof_clock() - c0; trace(p, 1, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.xa_off[buf], (uint32_t)sg.xa_rows, sg.n_items, sg.dil, false, false,
                            d1 + (uint32_t)((n % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k, 0u, 0u, c_t, 2 * s, w_seen, n);
@@ -377,10 +385,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         auto conv2s = [&](int n, int it, int s) {
             const PairSegP& sg = p.seg[s];
             long long c0 = 0;
-            if (prof) c0 = clock64();
+            if (prof) c0 = prof_clock();
             if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
             else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
-            if (prof) { c_d2 += clock64() - c0; trace(p, 2, n, 0); }
+            if (prof) { c_d2 += prof_clock() - c0; trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
                            true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
@@ -418,10 +426,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 if (++s2 == n_seg) { s2 = 0; ++it2; }
             }
         }
-        if (p.prof && (issuer == 0 || p.split)) {
+        if (PAIR_PROF && p.prof && (issuer == 0 || p.split)) {
             unsigned long long* o = p.prof + (size_t)blockIdx.x * 16;
             if (issuer == 0) {
-                o[0] = (unsigned long long)(clock64() - c_start);
+                o[0] = (unsigned long long)(prof_clock() - c_start);
                 o[1] = (unsigned long long)c_xa; o[2] = (unsigned long long)c_w;
             }
             if (issuer == 1 || !p.split) { o[3] = (unsigned long long)c_t; o[4] = (unsigned long long)c_d2; }
@@ -475,6 +483,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // On the critical path of every segment (conv2 cannot start before it ends): fully unrolled, two TMEM
         // loads in flight per warp.
         constexpr int UNITS = GROUPS * NB;               // (32-column group, row block) units per warp, two in flight
+        constexpr int EU = ND == 2 ? 1 : UNITS / 2;      // flat where e1 is on the critical path of every segment (ND = 1)
         const int q4 = warp & 3;                         // TMEM lane quarter this warp may read
         const int q = q4 * 32 + lane;                    // row inside a 128-row block
         const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
@@ -504,26 +513,26 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const TileCoord t = tile_of(p, it);
             for (int s = 0; s < n_seg; ++s, ++n) {
                 const int t0 = t.l0 - p.seg[s].h2 + q;   // sample index of this thread's operand row in block 0
-                const long long c0 = clock64();
+                const long long c0 = prof_clock();
                 const int nd = n % ND;                   // accumulator / operand buffer of this unit
                 mbar_wait(bar0 + 8u * (BAR_D1_FULL + nd), (uint32_t)((n / ND) & 1));
                 // split issue: the operand buffer of unit n - ND must have been read by its conv2 before it is rewritten
                 if (p.split && n >= ND) mbar_wait(bar0 + 8u * (BAR_T_EMPTY + nd), (uint32_t)((n / ND - 1) & 1));
-                const long long c1 = clock64();
+                const long long c1 = prof_clock();
                 c_wait += c1 - c0;
                 if (warp == PAIR_E1_WARP0) trace(p, 3, n, 0);
                 tc_fence_after();
                 const uint32_t t_acc = t_lane + (uint32_t)(nd * NB * C);
                 const uint32_t t_row = t_row0 + (uint32_t)nd * p.t_bytes;
-#pragma unroll
+#pragma unroll EU
                 for (int u = 0; u < UNITS; u += 2) {             // g-major unit order; both loads precede the wait
-                    const int g0 = u / NB, b0 = u % NB, g1 = (u + 1) / NB, b1 = (u + 1) % NB;
+                    const int g0 = u / NB, b0 = u % NB, g1 = (u + 1) / NB, b1 = (u + 1) % NB;   // not unrolled: compact code (see e2)
                     uint32_t ra[32], rb[32];
-                    const long long cl0 = clock64();
+                    const long long cl0 = prof_clock();
                     tmem_ld32(t_acc + (uint32_t)(b0 * C + g0 * 32), ra);
                     tmem_ld32(t_acc + (uint32_t)(b1 * C + g1 * 32), rb);
                     tmem_ld_wait();
-                    c_ld += clock64() - cl0;
+                    c_ld += prof_clock() - cl0;
                     const int r0 = t0 + b0 * 128, r1 = t0 + b1 * 128;      // conv2 zero-pads outside the utterance
                     if (!(p.dbg & 2)) {
                         convert(ra, t_row, g0, b0, r0 >= 0 && r0 < p.L);
@@ -550,13 +559,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                         else mbar_arrive(bar);
                     }
                 }
-                const long long c2 = clock64();
+                const long long c2 = prof_clock();
                 if (warp == PAIR_E1_WARP0) trace(p, 3, n, 1);
-                c_work += clock64() - c1;
-                c_fence += clock64() - c2;
+                c_work += prof_clock() - c1;
+                c_fence += prof_clock() - c2;
             }
         }
-        if (p.prof && warp == PAIR_E1_WARP0 && lane == 0) {
+        if (PAIR_PROF && p.prof && warp == PAIR_E1_WARP0 && lane == 0) {
             p.prof[(size_t)blockIdx.x * 16 + 5] = (unsigned long long)c_wait;
             p.prof[(size_t)blockIdx.x * 16 + 6] = (unsigned long long)c_work;
             p.prof[(size_t)blockIdx.x * 16 + 9] = (unsigned long long)c_ld;
@@ -569,6 +578,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // ncu source page showed a third of e2's stall samples as instruction fetch (stall_no_inst) -- in launches
         // where e2 is the busiest role (C <= 64).  Addresses are computed per chunk instead.
         constexpr int ITEMS = NB * GROUPS / 2;           // per warp
+        constexpr int JU = ITEMS > 2 ? ITEMS : 1;        // generic drain: flat where e2 is on the critical path between tiles (ND = 1)
         const int q4 = warp & 3;
         const int q = q4 * 32 + lane;
         const int half = warp >> 2;
@@ -638,6 +648,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 tmem_st16(d2u + (uint32_t)(blk * C + hc * 8), r);
             }
             tmem_st_wait();
+            if (warp == 0 && u >= ND) trace(p, 9, u - ND, 1);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
@@ -652,13 +663,14 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             load_res(tile_of(p, 0), 0);
         }
         for (int it = 0; it < p.iters; ++it) {
+            if (warp == 0) trace(p, 7, it * n_seg + n_seg - 1, 0);
             const TileCoord t = tile_of(p, it);
             const bool has_next = it + 1 < p.iters;
             const size_t e_tile = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8;   // chunk 0, block 0 row of this thread
-            const long long c0 = clock64();
+            const long long c0 = prof_clock();
             const int nd = it % ND;
             mbar_wait(bar0 + 8u * (BAR_D2_FULL + nd), (uint32_t)((it / ND) & 1));
-            const long long c1 = clock64();
+            const long long c1 = prof_clock();
             c_wait += c1 - c0;
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 0);
             tc_fence_after();
@@ -695,6 +707,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 for (int cc = 0; cc < 2 * ITEMS; cc += 2) {
                     chunk_geom(cc + 1, col, eb, okb);
                     tmem_ld_wait();
+                    if (warp == 0 && cc == 0) trace(p, 7, it, 1);
                     tmem_ld16(d2n + col, rb);
                     if (oka) store_chunk(ra, ea);
                     tmem_ld_wait();
@@ -705,10 +718,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     if (okb) store_chunk(rb, eb);
                 }
                 // this warp's part of D2[nd] is drained: initialise it for tile it + ND (init_d2 signals the issuer)
+                if (warp == 0) trace(p, 9, it, 0);
                 if (it + ND < p.iters) init_d2(it + ND);
             } else {
                 const TileCoord tn = tile_of(p, has_next ? it + 1 : it);
-#pragma unroll 1
+#pragma unroll JU
                 for (int j = 0; j < ITEMS; ++j) {
                     int blk, g, rel; bool ok;
                     item_geom(t, j, blk, g, rel, ok);
@@ -803,10 +817,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     }
                 }
             }
-            c_work += clock64() - c1;
+            c_work += prof_clock() - c1;
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 1);
         }
-        if (p.prof && warp == 0 && lane == 0) {
+        if (PAIR_PROF && p.prof && warp == 0 && lane == 0) {
             p.prof[(size_t)blockIdx.x * 16 + 7] = (unsigned long long)c_wait;
             p.prof[(size_t)blockIdx.x * 16 + 8] = (unsigned long long)c_work;
         }
@@ -1031,7 +1045,7 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     at[0].val.clusterDim.x = (unsigned)cg; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    static const bool prof_on = getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';
+    static const bool prof_on = PAIR_PROF && getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';   // experiments build only
 #ifdef VO2W_EXPERIMENTS
     // what-if timing switches (results are WRONG under VO2W_PAIR_DBG): only in builds made with -DVO2W_EXPERIMENTS, so a
     // stray environment variable can never corrupt the audio of the shipped library
@@ -1068,8 +1082,8 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
             const long long t0 = at(1, 16, 0);
             static const char* names[PAIR_TR_ROLES] = {"xa producer (idle, EMPTY seen)", "conv1 issue (start, done)", "conv2 issue (start, done)",
                                                        "e1 (D1 full seen, done)", "e2 (D2 full seen, done)", "w producer (request c1, c2)",
-                                                       "conv1 (W seen, items issued)", "conv1 (W_EMPTY committed, -)",
-                                                       "conv1 (before XA wait, XA local seen)", "conv1 (XA peer seen, W local seen)"};
+                                                       "conv1 (W seen, items issued)", "e2 (loop top, first tmem ld done)",
+                                                       "conv1 (before XA wait, XA local seen)", "e2 (drained, D2 init stored)"};
             for (int role = 0; role < PAIR_TR_ROLES; ++role) {
                 fprintf(stderr, "  [trace] %-32s", names[role]);
                 for (int u = 16; u < 28 && u < p.iters * p.n_seg; ++u)
