@@ -175,7 +175,11 @@ __device__ __forceinline__ void issue_conv(const PairP& p, const bool prof, int 
     }
 }
 
-template <int CG, int C, bool POST>
+// RINIT (= p.rinit, single-segment launches): the residual enters D2 by initialisation, see e2.  A template parameter so
+// that each launch kind carries only its own e2 code: the generic drain (three residual tiles in registers) sets the
+// register pressure of the whole kernel, and its spills were reloaded in every role's loop -- with 227 KB of the SM's
+// L1 configured as shared memory a spill reload is an L2 round trip (ncu: ~23 % of e2's stall samples at C = 32).
+template <int CG, int C, bool POST, bool RINIT>
 __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid_constant__ PairP p) {
     static_assert(!POST || C == 32, "conv_post rides the last stage only (32 channels: one TMEM load holds a whole row)");
     constexpr int NB = C >= 256 ? 1 : (C >= 64 ? 2 : 4);     // 128-row accumulator blocks per tile (2*NB*C <= 512 TMEM columns)
@@ -206,7 +210,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             if ((i >= BAR_T_FULL && i < BAR_T_FULL + 8) || (i >= BAR_D1_EMPTY && i < BAR_D1_EMPTY + 2)) cnt = CG * PAIR_E1_WARPS;
             else if (i >= BAR_D2_EMPTY && i < BAR_D2_EMPTY + 2) cnt = CG * PAIR_E2_WARPS;
             else if (by_issuers) cnt = p.split ? 1 : NI;
-            if (p.rinit && i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 4) cnt += PAIR_E2_WARPS;   // + this CTA's e2 warps (they read the tile)
+            if (RINIT && i >= BAR_XA_EMPTY && i < BAR_XA_EMPTY + 4) cnt += PAIR_E2_WARPS;   // + this CTA's e2 warps (they read the tile)
             else if (landed && CG == 2 && rank == 0) cnt = 2;
             mbar_init(bar0 + 8u * i, cnt);
         }
@@ -350,12 +354,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             long long c0 = 0;
             if (prof) c0 = prof_clock();
             // rinit: D2 arrives INITIALISED with the residual by the e2 warps (every tile, the first ones too)
-            if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
+            if (RINIT) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
             else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
             if (prof) { c_d2 += prof_clock() - c0; if (issuer == 0) trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, NI>(p, prof, issuer, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
-                           true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           true, s > 0 || RINIT, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
                            bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
             if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
             if (prof && issuer == 0) trace(p, 2, n, 1);
@@ -386,12 +390,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             const PairSegP& sg = p.seg[s];
             long long c0 = 0;
             if (prof) c0 = prof_clock();
-            if (p.rinit) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
+            if (RINIT) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND) & 1));
             else if (s == 0 && it >= ND) mbar_wait_cluster(bar0 + 8u * (BAR_D2_EMPTY + it % ND), (uint32_t)((it / ND - 1) & 1));
             if (prof) { c_d2 += prof_clock() - c0; trace(p, 2, n, 0); }
             tc_fence_after();
             issue_conv<CG, C, NB, KS, 1>(p, prof, 0, bar0, sm0 + p.t_off + (uint32_t)(n % ND) * p.t_bytes, (uint32_t)p.t_rows, sg.n_items, 1,
-                           true, s > 0 || p.rinit, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
+                           true, s > 0 || RINIT, d2 + (uint32_t)((it % ND) * NB * C), sm0 + p.ring_off, idesc, ones_lo, wit, c_w, sg.k,
                            bar0 + 8u * (BAR_T_FULL + 4 * (n % ND)), (uint32_t)((n / ND) & 1), c_t, 2 * s + 1, w_seen);
             mma_commit<CG>(bar0 + 8u * (BAR_T_EMPTY + n % ND));          // operand buffer reusable once these MMAs retire
             if (s == n_seg - 1) mma_commit<CG>(bar0 + 8u * (BAR_D2_FULL + it % ND));
@@ -621,7 +625,6 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // (row block, column group) items it has just drained, so there is no cross-warp hazard on D2; the input tile is
         // released (XA_EMPTY) by conv1's commit plus these warps' arrivals.
         // Both directions walk this warp's columns in 16-column chunks: chunk cc = half (cc & 1) of item cc >> 1.
-        const bool rinit = p.rinit != 0;
         const uint32_t xa_empty_local = bar0 + 8u * BAR_XA_EMPTY;
         auto init_d2 = [&](int u) {
             const int use = u / p.xa_bufs, buf = u - use * p.xa_bufs, ndu = u % ND;
@@ -657,7 +660,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 else mbar_arrive(d2_empty_addr + 8u * (uint32_t)ndu);
             }
         };
-        if (rinit) {
+        if constexpr (RINIT) {
             for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
         } else if (p.iters > 0) {
             load_res(tile_of(p, 0), 0);
@@ -675,7 +678,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             if (warp == 0) trace(p, 4, it * n_seg + n_seg - 1, 0);
             tc_fence_after();
             const uint32_t d2n = t_lane + (uint32_t)((ND + nd) * NB * C);
-            if (rinit) {
+            if constexpr (RINIT) {
                 // residual already inside D2: drain = activation, bf16, store.  The load of chunk cc + 1 is in flight
                 // while chunk cc is converted and stored.
                 auto chunk_geom = [&](int cc, uint32_t& col, size_t& e, bool& ok) {
@@ -998,10 +1001,15 @@ int pair_plan(PairP& p, int C, int n_seg, const int* ks, const int* dils, int cg
 }
 
 typedef void (*pair_kernel_t)(const PairP);
-static pair_kernel_t pair_kernel_for(int cg, int C, bool post = false) {
-    if (post) return pair_umma_kernel<2, 32, true>;
-    if (cg == 2) return C == 256 ? pair_umma_kernel<2, 256, false> : (C == 128 ? pair_umma_kernel<2, 128, false> : (C == 64 ? pair_umma_kernel<2, 64, false> : pair_umma_kernel<2, 32, false>));
-    return C == 256 ? pair_umma_kernel<1, 256, false> : (C == 128 ? pair_umma_kernel<1, 128, false> : (C == 64 ? pair_umma_kernel<1, 64, false> : pair_umma_kernel<1, 32, false>));
+template <int CG, bool RINIT>
+static pair_kernel_t pair_kernel_c(int C) {
+    return C == 256 ? pair_umma_kernel<CG, 256, false, RINIT> : (C == 128 ? pair_umma_kernel<CG, 128, false, RINIT>
+         : (C == 64 ? pair_umma_kernel<CG, 64, false, RINIT> : pair_umma_kernel<CG, 32, false, RINIT>));
+}
+static pair_kernel_t pair_kernel_for(int cg, int C, bool post, bool rinit) {
+    if (post) return pair_umma_kernel<2, 32, true, false>;
+    if (cg == 2) return rinit ? pair_kernel_c<2, true>(C) : pair_kernel_c<2, false>(C);
+    return rinit ? pair_kernel_c<1, true>(C) : pair_kernel_c<1, false>(C);
 }
 
 int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream_t st) {
@@ -1011,8 +1019,9 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     if (!attr_set[cur]) {
         for (int cgi = 1; cgi <= 2; ++cgi)
             for (int c = 32; c <= 256; c *= 2)
-                VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(cgi, c), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
-        VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(2, 32, true), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
+                for (int ri = 0; ri < 2; ++ri)
+                    VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(cgi, c, false, ri != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
+        VO2W_CUDA_OK(cudaFuncSetAttribute(pair_kernel_for(2, 32, true, false), cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_LIMIT));
         attr_set[cur] = true;
     }
     const bool post = io.post_w != nullptr;
@@ -1058,7 +1067,7 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
         VO2W_CUDA_OK(cudaMalloc(&p.prof, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8));
         VO2W_CUDA_OK(cudaMemsetAsync(p.prof, 0, ((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2) * 8, st));
     }
-    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C, post), p));
+    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, pair_kernel_for(cg, p.C, post, p.rinit != 0), p));
     if (prof_on) {   // debug aid: per-role cycle accounting, averaged over the CTAs that recorded it
         std::vector<unsigned long long> h((size_t)grid * 16 + PAIR_TR_ROLES * PAIR_TR_UNITS * 2);
         VO2W_CUDA_OK(cudaStreamSynchronize(st));
