@@ -605,16 +605,21 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             rel = blk == 0 ? 0 : blk * 128 - back;
             ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
         };
-        auto load_res = [&](const TileCoord& t, int j) {    // all segments of item j into R[s]
+        auto load_res = [&](const TileCoord& t, int j, int hh) {   // half hh (16 columns) of item j, all segments, into R[s][2 hh ..]
             int blk, g, rel; bool ok;
             item_geom(t, j, blk, g, rel, ok);
             if (!ok) return;
-            const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
+            const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4 + hh * 2) * e_step;
 #pragma unroll
             for (int s = 0; s < PAIR_MAX_SEG; ++s)
                 if (s < n_seg) {
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) R[s][h] = __ldg((const uint4*)(p.seg[s].xa + e + (size_t)h * e_step));
+                    if (hh == 0) {
+                        R[s][0] = __ldg((const uint4*)(p.seg[s].xa + e));
+                        R[s][1] = __ldg((const uint4*)(p.seg[s].xa + e + e_step));
+                    } else {
+                        R[s][2] = __ldg((const uint4*)(p.seg[s].xa + e));
+                        R[s][3] = __ldg((const uint4*)(p.seg[s].xa + e + e_step));
+                    }
                 }
         };
         // Residual by initialisation (p.rinit: single-segment launches).  y = x + conv2(...): instead of fetching x again
@@ -663,7 +668,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         if constexpr (RINIT) {
             for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
         } else if (p.iters > 0) {
-            load_res(tile_of(p, 0), 0);
+            const TileCoord t0 = tile_of(p, 0);
+            load_res(t0, 0, 0);
+            load_res(t0, 0, 1);
         }
         for (int it = 0; it < p.iters; ++it) {
             if (warp == 0) trace(p, 7, it * n_seg + n_seg - 1, 0);
@@ -729,65 +736,68 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 for (int j = 0; j < ITEMS; ++j) {
                     int blk, g, rel; bool ok;
                     item_geom(t, j, blk, g, rel, ok);
-                    uint32_t r[32];
-                    tmem_ld32(d2n + (uint32_t)(blk * C + g * 32), r);
-                    tmem_ld_wait();
-                    float v[32];
+                    // An item is drained in two halves of 16 columns: 16 live accumulator registers next to the 48 of R
+                    // (with a 32-column load this path spilled, and the spills were reloaded in every loop of the kernel).
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]);
-                    // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
-                    auto add_res = [&](const uint4 (&x)[4]) {
+                    for (int hh = 0; hh < 2; ++hh) {
+                        uint32_t r[16];
+                        tmem_ld16(d2n + (uint32_t)(blk * C + g * 32 + hh * 16), r);
+                        tmem_ld_wait();
+                        float v[16];
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) {
-                            const uint32_t w[4] = {x[h].x, x[h].y, x[h].z, x[h].w};
+                        for (int c = 0; c < 16; ++c) v[c] = __uint_as_float(r[c]);
+                        // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
+                        auto add_res = [&](const uint4& x0, const uint4& x1) {
+                            const uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) {
+                            for (int i = 0; i < 8; ++i) {
                                 const float2 f = unpack_bf16x2(w[i]);
-                                v[h * 8 + 2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[h * 8 + 2 * i] + f.x);
-                                v[h * 8 + 2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[h * 8 + 2 * i + 1] + f.y);
+                                v[2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[2 * i] + f.x);
+                                v[2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[2 * i + 1] + f.y);
                             }
+                        };
+                        if (ok) {
+#pragma unroll
+                            for (int s = 0; s < PAIR_MAX_SEG; ++s)
+                                if (s < n_seg) add_res(R[s][2 * hh], R[s][2 * hh + 1]);
                         }
-                    };
-                    if (ok) {
+                        // the registers are free again: fetch what uses them next (the same half of the next item, or of
+                        // the next tile's first item) while this half is scaled and stored
+                        if (j + 1 < ITEMS) load_res(t, j + 1, hh);
+                        else if (has_next) load_res(tn, 0, hh);
+                        if (ok) {
+                            // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
-                        for (int s = 0; s < PAIR_MAX_SEG; ++s)
-                            if (s < n_seg) add_res(R[s]);
-                    }
-                    // the registers are free again: fetch what uses them next while this item is scaled and stored
-                    if (j + 1 < ITEMS) load_res(t, j + 1);
-                    else if (has_next) load_res(tn, 0);
-                    if (ok) {
-                        // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
+                            for (int c = 0; c < 16; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
+                        }
+                        if constexpr (POST) {
+                            // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
+                            // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
+                            // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory
+                            // (the second half adds to the first's); the taps are summed across rows after the tile's
+                            // barrier.  Rows outside the utterance are conv_post's zero padding.  x is never written to HBM.
+                            if (blk > 0 || q < 128 - back) {
+                                float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
-                    }
-                    if constexpr (POST) {
-                        // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
-                        // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
-                        // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory;
-                        // the taps are summed across rows after the tile's barrier.  Rows outside the utterance are
-                        // conv_post's zero padding.  x is never written to HBM.
-                        if (blk > 0 || q < 128 - back) {
-                            float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
+                                for (int jj = 0; jj < PAIR_POST_K; ++jj) {
+                                    float a = hh == 0 ? 0.f : pr[jj * PAIR_POST_ROWS];
+                                    if (ok) {
 #pragma unroll
-                            for (int jj = 0; jj < PAIR_POST_K; ++jj) {
-                                float a = 0.f;
-                                if (ok) {
-#pragma unroll
-                                    for (int c = 0; c < 32; ++c) a = fmaf(v[c], p.post_w[jj * 32 + c], a);
+                                        for (int c = 0; c < 16; ++c) a = fmaf(v[c], p.post_w[jj * 32 + hh * 16 + c], a);
+                                    }
+                                    pr[jj * PAIR_POST_ROWS] = a;
                                 }
-                                pr[jj * PAIR_POST_ROWS] = a;
                             }
-                        }
-                    } else if (ok) {
-                        const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4) * e_step;
-                        // out = bf16(...), one rounding
+                        } else if (ok) {
+                            const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4 + hh * 2) * e_step;
+                            // out = bf16(...), one rounding
 #pragma unroll
-                        for (int h = 0; h < 4; ++h) {
-                            uint4 o;
-                            o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
-                            o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
-                            *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
+                            for (int h = 0; h < 2; ++h) {
+                                uint4 o;
+                                o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
+                                o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
+                                *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
+                            }
                         }
                     }
                 }
