@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
 
@@ -37,6 +38,11 @@ static inline int vo2w_ceil_div(long long a, long long b) { return (int)((a + b 
 
 // One-time per-DEVICE setup (cudaFuncSetAttribute, SM count): function attributes belong to the device's context, so a
 // process that drives several GPUs must set them once per device, not once per process.
+// Programmatic dependent launch of the persistent tcgen05 kernels (pair_umma.cu, stream_umma.cu); VO2W_PDL=0 disables it.
+static inline bool vo2w_pdl_enabled() {
+    static const bool on = !(getenv("VO2W_PDL") && getenv("VO2W_PDL")[0] == '0');
+    return on;
+}
 #define VO2W_MAX_DEV 64
 static inline int vo2w_cur_dev() {
     int d = 0;

@@ -216,6 +216,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         }
         fence_mbar_init();
     }
+    // the next kernel of the stream may be scheduled as soon as SMs free up (its set-up overlaps this grid's tail)
+    if (threadIdx.x == 0) griddep_launch_dependents();
     if (warp == PAIR_WARP_TMEM) tmem_alloc_cg<CG>(smem_u32(&tmem_base_s), 512u);
     // A operand of the bias MMA: 128 rows x K=16 with ones in the first two K columns (bias = hi + lo in bf16)
     if (threadIdx.x < 256)
@@ -245,6 +247,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 const __nv_bfloat16* src = sg.xa + ((size_t)t.b * chunks * p.Lp + start) * 8;
                 for (int c = 0; c < chunks; ++c) prefetch_l2(src + (size_t)c * p.Lp * 8, (uint32_t)rows * 16u);
             };
+            griddep_wait();                              // the input is the previous launch's output
             for (int m = 2; m < 2 + p.pf; ++m) prefetch_unit(m);
             int n = 0;                                   // running (tile, segment) counter -> buffer and phase
             for (int it = 0; it < p.iters; ++it) {
@@ -668,6 +671,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         if constexpr (RINIT) {
             for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
         } else if (p.iters > 0) {
+            griddep_wait();                              // the residual rows are read straight from the previous launch's output
             const TileCoord t0 = tile_of(p, 0);
             load_res(t0, 0, 0);
             load_res(t0, 0, 1);
@@ -1059,11 +1063,13 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     cfg.blockDim = dim3(PAIR_THREADS);
     cfg.dynamicSmemBytes = p.smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)cg; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;     // see griddep_wait(); VO2W_PDL=0 turns it off
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = vo2w_pdl_enabled() ? 2 : 1;
     static const bool prof_on = PAIR_PROF && getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';   // experiments build only
 #ifdef VO2W_EXPERIMENTS
     // what-if timing switches (results are WRONG under VO2W_PAIR_DBG): only in builds made with -DVO2W_EXPERIMENTS, so a

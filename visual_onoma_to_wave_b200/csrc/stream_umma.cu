@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             mbar_init(bar0 + 8u * i, (i >= SB_ACC_EMPTY && i < SB_ACC_EMPTY + 2) ? 2 * SU_EPI_WARPS : 1);
         fence_mbar_init();
     }
+    if (threadIdx.x == 0) griddep_launch_dependents();   // programmatic dependent launch, see umma_cg.cuh
     if (warp == 3) tmem_alloc_cg<2>(smem_u32(&tmem_base_s), 512u);
     tc_fence_before();
     __syncthreads();
@@ -94,6 +95,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
     if (warp == 0) {
         // ================= input tile producer =================
         if (lane == 0) {
+            griddep_wait();                              // the input is the previous launch's output
             int n = 0;
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
                 const SuTile t = su_tile(p, v, (int)rank);
@@ -606,11 +608,13 @@ int su_launch(const SuLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out, flo
     cfg.blockDim = dim3(SU_THREADS);
     cfg.dynamicSmemBytes = p.smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = vo2w_pdl_enabled() ? 2 : 1;
     VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, stream_umma_kernel, p));
     return VO2W_OK;
 }
