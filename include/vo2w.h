@@ -247,8 +247,8 @@ int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8_t* mask, i
  * libvo2w.so until the process exits); the call makes no cudaMalloc / cudaFree and uses no allocating library routine.
  * Same arguments, results (bit-identical: the same kernels run) and errors as vo2w_varpred_forward, plus:
  *   - VO2W_E_WORKSPACE when vo2w_varpred_workspace_bytes(p, B, T) > VO2W_VARPRED_STATIC_BYTES, i.e. when
- *     B * T * 4 * (d_in + 2 * d_filter) (each term rounded up to 256 bytes) exceeds 8 MiB -- 2730 tokens for the
- *     reference's d_in = d_filter = 256;
+ *     B * (T + 2) * (4 * (d_in + 2 * d_filter) + 1) (each term rounded up to 256 bytes) exceeds 8 MiB -- about 2700
+ *     tokens for the reference's d_in = d_filter = 256 (B = 16 x T = 168);
  *   - the first call on a device looks the array's address up (cudaGetSymbolAddress, with the caller's current device):
  *     make it outside graph capture;
  *   - every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to

@@ -6,19 +6,23 @@
 //       re-normalised; x + embedding[bucketize(value, bins)]
 //   duration rounding (modules.py:110-113):  clamp(round(exp(log_d) - 1) * d_control, min=0)
 //
-// fp32 CUDA-core path, channel-major like the decoder: the two convolutions ride conv_simt.cu, relu is folded into the
-// LayerNorm kernel's load, the final projection and the mask are one small kernel.  The affine steps around the
+// The predictor's two convolutions run on the tensor pipe with fp32-level accuracy (conv_tf32.cu), time-major, with the
+// utterances laid end to end (frame_rows_kernel); shapes that kernel does not tile take the fp32 CUDA-core path
+// (channel-major, conv_simt.cu, relu folded into the LayerNorm kernel's load).  The affine steps around the
 // bucket search use explicit round-to-nearest multiplies / adds / divides (no FMA contraction) so that a value sits on
 // the same side of a bin edge as in the reference's fp32 arithmetic.
 #include <mutex>
 #include <vector>
 
 #include "conv_simt.cuh"
+#include "conv_tf32.cuh"
 #include "rows.cuh"
 
 struct vo2w_varpred {
     int d_in = 0, d_filter = 0, k = 0;
     float* w_dev = nullptr;
+    float* p_dev = nullptr;      // both convolutions packed for tf32_conv_kernel (null: shapes it does not tile -> CUDA cores)
+    size_t p2 = 0;               // offset of the second convolution inside p_dev
     size_t w1, b1, g1, be1, w2, b2, g2, be2, wl, bl;
 };
 
@@ -43,6 +47,37 @@ __global__ void __launch_bounds__(256) project_mask_kernel(const float* __restri
         for (int i = 0; i < 8; ++i) v += red[i][tl];
         out[(size_t)b * L + l] = (mask && mask[(size_t)b * L + l]) ? 0.f : v;
     }
+}
+
+// Tensor-pipe path: the B utterances are laid end to end as ONE sequence of B * (T + 2) rows, every utterance framed by a
+// zero row on either side (= the convolutions' zero padding), so that the 128-row tiles of tf32_conv_kernel are full
+// whatever T is (the reference's T_src is ~32).  xp[b * (T + 2) + 1 + t] = x[b, t]; pad[r] = 1 on the framing rows.
+__global__ void __launch_bounds__(256) frame_rows_kernel(const float* __restrict__ x, float* __restrict__ xp,
+                                                         uint8_t* __restrict__ pad, int T, int C4, long long rows_p) {
+    const long long r = (long long)blockIdx.x * 4 + (threadIdx.x >> 6);       // 64 threads per row
+    if (r >= rows_p) return;
+    const int t = (int)(r % (T + 2)) - 1;
+    const long long b = r / (T + 2);
+    const bool framing = t < 0 || t >= T;
+    float4* o = reinterpret_cast<float4*>(xp) + (size_t)r * C4;
+    const float4* i = reinterpret_cast<const float4*>(x) + (size_t)(b * T + (framing ? 0 : t)) * C4;
+    for (int c = threadIdx.x & 63; c < C4; c += 64) o[c] = framing ? make_float4(0.f, 0.f, 0.f, 0.f) : i[c];
+    if ((threadIdx.x & 63) == 0) pad[r] = framing ? 1 : 0;
+}
+
+// one warp per row (b,t); x is the framed sequence [B * (T + 2), C]
+__global__ void __launch_bounds__(256) project_mask_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                                const float* __restrict__ bias, const uint8_t* __restrict__ mask,
+                                                                float* __restrict__ out, long long rows, int T, int C) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const float* xr = x + (size_t)(r + 2 * (r / T) + 1) * C;
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc = fmaf(w[c], xr[c], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) out[r] = (mask && mask[r]) ? 0.f : acc + bias[0];
 }
 
 // one warp per (b,t) row: bucket search on lane 0's value, then the embedding row is added to x
@@ -150,6 +185,27 @@ extern "C" int vo2w_varpred_create(int d_in, int d_filter, int k, const float* b
         delete p;
         return VO2W_E_CUDA;
     }
+    // Tensor pipe with fp32-level accuracy (conv_tf32.cu, as the decoder and PostNet) where the kernel tiles the shapes
+    // (the reference's 256 -> 256 -> 256, k = 3, does): time-major, so nothing is transposed.
+    if (tf32_conv_supported(d_filter, d_in, k) && tf32_conv_supported(d_filter, d_filter, k)) {
+        p->p2 = tf32_conv_packed_floats(d_filter, d_in, k);
+        const size_t total = p->p2 + tf32_conv_packed_floats(d_filter, d_filter, k);
+        if (cudaMalloc(&p->p_dev, total * 4) != cudaSuccess) {
+            vo2w_set_error("varpred_create: allocating packed weights failed");
+            vo2w_varpred_destroy(p);
+            return VO2W_E_CUDA;
+        }
+        if ((rc = tf32_conv_pack(p->w_dev + p->w1, d_filter, d_in, k, p->p_dev, 0)) != VO2W_OK ||
+            (rc = tf32_conv_pack(p->w_dev + p->w2, d_filter, d_filter, k, p->p_dev + p->p2, 0)) != VO2W_OK) {
+            vo2w_varpred_destroy(p);
+            return rc;
+        }
+        if (cudaDeviceSynchronize() != cudaSuccess) {
+            vo2w_set_error("varpred_create: packing weights failed");
+            vo2w_varpred_destroy(p);
+            return VO2W_E_CUDA;
+        }
+    }
     *out = p;
     return VO2W_OK;
 }
@@ -157,14 +213,15 @@ extern "C" int vo2w_varpred_create(int d_in, int d_filter, int k, const float* b
 extern "C" int vo2w_varpred_destroy(vo2w_varpred* p) {
     if (!p) return VO2W_OK;
     if (p->w_dev) cudaFree(p->w_dev);
+    if (p->p_dev) cudaFree(p->p_dev);
     delete p;
     return VO2W_OK;
 }
 
 extern "C" size_t vo2w_varpred_workspace_bytes(const vo2w_varpred* p, int B, int T) {
     if (!p || B <= 0 || T <= 0) return 0;
-    const size_t bt = (size_t)B * T * 4;
-    return var_align(bt * p->d_in) + 2 * var_align(bt * p->d_filter);
+    const size_t rows = (size_t)B * (T + 2);        // every utterance framed by two zero rows (tensor-pipe path)
+    return var_align(rows * 4 * p->d_in) + 2 * var_align(rows * 4 * p->d_filter) + var_align(rows);
 }
 
 extern "C" int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8_t* mask, int B, int T, float* out,
@@ -178,12 +235,31 @@ extern "C" int vo2w_varpred_forward(vo2w_varpred* p, const float* x, const uint8
     }
     cudaStream_t st = (cudaStream_t)stream;
     const int F = p->d_filter;
-    const size_t bt = (size_t)B * T * 4;
+    const size_t bt = (size_t)B * (T + 2) * 4;
     uint8_t* ws = (uint8_t*)workspace;
     float* xn = (float*)ws;
     float* a = (float*)(ws + var_align(bt * p->d_in));
     float* b = (float*)(ws + var_align(bt * p->d_in) + var_align(bt * F));
+    uint8_t* pad = ws + var_align(bt * p->d_in) + 2 * var_align(bt * F);
     const float* W = p->w_dev;
+    const long long rows_p = (long long)B * (T + 2);
+    if (p->p_dev && rows_p < (1ll << 31) && (((uintptr_t)x) & 15) == 0) {
+        // relu is the convolution kernel's activation; LayerNorm runs on its time-major rows and zeroes the framing
+        // rows again (the reference itself masks only the final projection, modules.py:205-211)
+        frame_rows_kernel<<<(unsigned)vo2w_ceil_div(rows_p, 4), 256, 0, st>>>(x, xn, pad, T, p->d_in / 4, rows_p);
+        VO2W_CUDA_OK(cudaGetLastError());
+        Tf32Conv c1{xn, p->p_dev, W + p->b1, nullptr, a, 1, (int)rows_p, p->d_in, F, p->k, 1};
+        int rc = tf32_conv1d(c1, st);
+        if (rc != VO2W_OK) return rc;
+        if ((rc = rows_layernorm_mask(a, W + p->g1, W + p->be1, pad, b, rows_p, F, st)) != VO2W_OK) return rc;
+        Tf32Conv c2{b, p->p_dev + p->p2, W + p->b2, nullptr, a, 1, (int)rows_p, F, F, p->k, 1};
+        if ((rc = tf32_conv1d(c2, st)) != VO2W_OK) return rc;
+        if ((rc = rows_layernorm_mask(a, W + p->g2, W + p->be2, pad, b, rows_p, F, st)) != VO2W_OK) return rc;
+        const long long rows = (long long)B * T;
+        project_mask_rows_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(b, W + p->wl, W + p->bl, mask, out, rows, T, F);
+        VO2W_CUDA_OK(cudaGetLastError());
+        return VO2W_OK;
+    }
     dim3 grid((unsigned)vo2w_ceil_div(T, 32), (unsigned)B);
     int rc = rows_transpose_add(x, nullptr, xn, B, T, p->d_in, st);
     if (rc != VO2W_OK) return rc;
