@@ -70,9 +70,9 @@ __device__ __forceinline__ TileCoord tile_of(const PairP& p, int it) {
     return t;
 }
 
-// Cycle accounting and event traces exist only in the experiments build (-DVO2W_EXPERIMENTS): the product kernel carries
-// no clock reads and no counters (they cost registers in roles that already spill).
-#ifdef VO2W_EXPERIMENTS
+// Cycle accounting and event traces exist only in builds made with -DVO2W_PAIR_PROFILE: the product kernel (and the
+// experiments build with its what-if switches) carries no clock reads and no counters -- they cost registers.
+#ifdef VO2W_PAIR_PROFILE
 constexpr bool PAIR_PROF = true;
 #else
 constexpr bool PAIR_PROF = false;
@@ -1070,7 +1070,7 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = vo2w_pdl_enabled() ? 2 : 1;
-    static const bool prof_on = PAIR_PROF && getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';   // experiments build only
+    static const bool prof_on = PAIR_PROF && getenv("VO2W_PAIR_PROF") && getenv("VO2W_PAIR_PROF")[0] == '1';   // -DVO2W_PAIR_PROFILE builds only
 #ifdef VO2W_EXPERIMENTS
     // what-if timing switches (results are WRONG under VO2W_PAIR_DBG): only in builds made with -DVO2W_EXPERIMENTS, so a
     // stray environment variable can never corrupt the audio of the shipped library
