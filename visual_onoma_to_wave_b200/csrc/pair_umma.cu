@@ -10,16 +10,20 @@
 // matrices, any 16-byte aligned start address), so dilation halos cost no copies.
 //
 // One persistent CTA (CG=1) or CTA pair (CG=2, tcgen05 cta_group::2, M=256 = 2 x 128 rows, the weight
-// operand split N/2 per CTA) walks tiles of NB x 128 rows of one utterance.  Per tile and segment:
-//   warp 0  lane 0: bulk-copies the input tile (128*NB + 2*h1 rows, all channels) into shared memory and
-//                   prefetches the residual rows into L2
-//   warp 2  lane 0: streams packed weights through an mbarrier ring (every stage is used by all NB row blocks)
-//   warp 1        : leader CTA: one elected lane issues every tcgen05.mma of both convolutions;
-//                   peer CTA: relays its "bytes have landed" barriers to the leader
-//   warps 4-7     : e1: D1 (TMEM) + b1 -> lrelu -> bf16 -> shared memory (the conv2 operand never leaves the SM)
-//   warps 8-15    : e2 (after the last segment): D2 + sum b2 + sum residuals -> bf16 stream(s) in HBM
-// Accumulators: D1[NB], D2[NB] in TMEM (2*NB*C <= 512 columns); conv2 of all segments accumulates into D2.
-// e2 of a tile overlaps the MMAs of the next tile; e1 is on the critical path of its segment.
+// operand split N/2 per CTA) walks tiles of NB x 128 rows of one utterance.  Warp roles (pair_umma.cuh), per tile and segment:
+//   warp 12 lane 0: bulk-copies the input tile (128*NB + 2*h1 rows, all channels) into one of up to 4 shared-memory
+//                   buffers and prefetches later tiles into L2
+//   warp 13 lane 0: packed weights: copied once per kernel where a launch's convolutions fit shared memory (C <= 64),
+//                   else streamed through an mbarrier ring (every stage is used by all NB row blocks)
+//   warps 14-15   : leader CTA: one elected thread per warp issues tcgen05.mma (split issue: warp 14 every conv1, warp 15
+//                   every conv2; else both walk the same schedule and split the row blocks);
+//                   peer CTA: warp 14 relays its "bytes have landed" barriers to the leader
+//   warps 8-11    : e1: D1 (TMEM) + b1 -> lrelu -> bf16 -> shared memory (the conv2 operand never leaves the SM)
+//   warps 0-7     : e2 (after the last segment): D2 + sum b2 + sum residuals -> bf16 stream in HBM (or conv_post + tanh
+//                   -> waveform); single-segment launches: the residual is written INTO D2 before conv2 (RINIT)
+// Accumulators: ND copies of D1[NB], D2[NB] in TMEM (2*ND*NB*C <= 512 columns; ND = 2 for C <= 64: conv1 of unit n+1
+// is issued before conv2 of unit n); conv2 of all segments accumulates into D2.  e2 of a tile overlaps the MMAs of the
+// next tile; e1 is on the critical path of its segment where ND = 1.
 #include "pair_umma.cuh"
 #include "umma_cg.cuh"
 
