@@ -38,11 +38,18 @@ static inline int vo2w_ceil_div(long long a, long long b) { return (int)((a + b 
 
 // One-time per-DEVICE setup (cudaFuncSetAttribute, SM count): function attributes belong to the device's context, so a
 // process that drives several GPUs must set them once per device, not once per process.
-// Programmatic dependent launch of the persistent tcgen05 kernels (pair_umma.cu, stream_umma.cu); VO2W_PDL=0 disables it.
+// Programmatic dependent launch of the tcgen05 kernels (pair_umma.cu, stream_umma.cu, conv_tf32.cu); VO2W_PDL=0 disables it.
 static inline bool vo2w_pdl_enabled() {
     static const bool on = !(getenv("VO2W_PDL") && getenv("VO2W_PDL")[0] == '0');
     return on;
 }
+#ifdef __CUDACC__
+// Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
+// (barrier set-up, TMEM allocation, weight loads) while the previous kernel of the stream is draining; it must not
+// touch that kernel's results before griddep_wait() returns (= the previous grid has completed and flushed).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
 #define VO2W_MAX_DEV 64
 static inline int vo2w_cur_dev() {
     int d = 0;

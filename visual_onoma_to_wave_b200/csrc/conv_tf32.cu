@@ -106,11 +106,15 @@ __global__ void __launch_bounds__(T32_THREADS) tf32_conv_kernel(const __grid_con
         mbar_init(acc_full, 1);
         fence_mbar_init();
     }
+    if (threadIdx.x == 0) griddep_launch_dependents();   // programmatic dependent launch (common.cuh): the next kernel of
+                                                         // the stream may set up on SMs this grid has left
     if (warp == 9) tmem_alloc(smem_u32(&tmem_base_s), p.tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
+    griddep_wait();                                      // activations, residuals (and, in attention, the packed operand) are
+                                                         // the previous kernels' outputs
 
     if (warp < 8) {
         // ===================== activation producers: global fp32 -> hi/lo core matrices =====================
@@ -329,9 +333,17 @@ int launch(const T32K& kp, size_t smem, cudaStream_t st) {
         VO2W_CUDA_OK(cudaFuncSetAttribute(tf32_conv_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
         attr[cur] = true;
     }
-    dim3 grid((unsigned)vo2w_ceil_div(kp.c.L, 128 * NB), (unsigned)kp.n_tiles, (unsigned)(kp.c.B * kp.c.heads));
-    tf32_conv_kernel<NB><<<grid, T32_THREADS, smem, st>>>(kp);
-    VO2W_CUDA_OK(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)vo2w_ceil_div(kp.c.L, 128 * NB), (unsigned)kp.n_tiles, (unsigned)(kp.c.B * kp.c.heads));
+    cfg.blockDim = dim3(T32_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = vo2w_pdl_enabled() ? 1 : 0;
+    VO2W_CUDA_OK(cudaLaunchKernelEx(&cfg, tf32_conv_kernel<NB>, kp));
     return VO2W_OK;
 }
 

@@ -148,11 +148,6 @@ __device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t v, __nv_bfloat162 slop
     const __nv_bfloat162 r = __hmax2(a, __hmul2(a, slope2));
     return *reinterpret_cast<const uint32_t*>(&r);
 }
-// Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
-// (barrier set-up, TMEM allocation, weight loads) while the previous kernel of the stream is draining; it must not
-// touch that kernel's results before griddep_wait() returns (= the previous grid has completed and flushed).
-__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_l2(const void* p, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
