@@ -33,10 +33,10 @@ namespace {
 enum {
     SB_A_FULL = 0,                          // [SU_A_BUFS] input tile landed (complete_tx)
     SB_A_EMPTY = SB_A_FULL + SU_A_BUFS,     // every MMA of the unit has read it (tcgen05.commit, both CTAs)
-    SB_A_FULL_PEER = SB_A_EMPTY + SU_A_BUFS,   // leader only: the peer's tile landed
+    SB_A_FULL_PEER = SB_A_EMPTY + SU_A_BUFS,   // (unused: the peer's relay arrives on the leader's SB_A_FULL)
     SB_W_FULL = SB_A_FULL_PEER + SU_A_BUFS, // [SU_SLOTS]
     SB_W_EMPTY = SB_W_FULL + SU_SLOTS,
-    SB_W_FULL_PEER = SB_W_EMPTY + SU_SLOTS, // leader only
+    SB_W_FULL_PEER = SB_W_EMPTY + SU_SLOTS, // (unused, as above)
     SB_ACC_FULL = SB_W_FULL_PEER + SU_SLOTS,   // [2] accumulator buffer complete (commit, both CTAs)
     SB_ACC_EMPTY = SB_ACC_FULL + 2,         // [2] leader only: all epilogue warps of the pair have read the buffer
     SB_COUNT = SB_ACC_EMPTY + 2
@@ -77,8 +77,12 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
     const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < SB_COUNT; ++i)
-            mbar_init(bar0 + 8u * i, (i >= SB_ACC_EMPTY && i < SB_ACC_EMPTY + 2) ? 2 * SU_EPI_WARPS : 1);
+        for (int i = 0; i < SB_COUNT; ++i) {
+            // "landed" barriers of the LEADER collect two arrivals per phase: its own producer's (with the byte count) and
+            // the peer CTA's relay, so the issuer waits once per operand (as pair_umma_kernel does)
+            const bool landed = (i >= SB_A_FULL && i < SB_A_FULL + SU_A_BUFS) || (i >= SB_W_FULL && i < SB_W_FULL + SU_SLOTS);
+            mbar_init(bar0 + 8u * i, (i >= SB_ACC_EMPTY && i < SB_ACC_EMPTY + 2) ? 2 * SU_EPI_WARPS : ((landed && rank == 0) ? 2 : 1));
+        }
         fence_mbar_init();
     }
     if (threadIdx.x == 0) griddep_launch_dependents();   // programmatic dependent launch, see umma_cg.cuh
@@ -154,8 +158,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             int n = 0;
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
                 const int use = n / a_bufs, buf = n - use * a_bufs;
-                mbar_wait(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));
-                mbar_wait_cluster(bar0 + 8u * (SB_A_FULL_PEER + buf), (uint32_t)(use & 1));
+                mbar_wait_cluster(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));   // both CTAs' tiles
                 tc_fence_after();
                 const uint32_t a_base = (((sm0 + p.a_off[buf]) >> 4) & 0x3FFFu) | (a_rows << 16);   // LBO = a_rows * 16 B
                 const int ng = v / p.pair_m;
@@ -176,8 +179,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                             if (w_wait) {
                                 slot = wit & slot_mask;
                                 const uint32_t par = (wit >> slot_log2) & 1u;
-                                mbar_wait(bar0 + 8u * (SB_W_FULL + slot), par);
-                                mbar_wait_cluster(bar0 + 8u * (SB_W_FULL_PEER + slot), par);
+                                mbar_wait_cluster(bar0 + 8u * (SB_W_FULL + slot), par);           // both CTAs' halves
                                 tc_fence_after();
                             } else {
                                 slot = (uint32_t)(tt * stages_per_tile + s);     // resident: stage index == slot
@@ -214,12 +216,12 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
             for (int v = pair; v < p.n_units; v += n_pairs, ++n) {
                 const int use = n / a_bufs, buf = n - use * a_bufs;
                 mbar_wait(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));
-                mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_A_FULL_PEER + buf), 0));
+                mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_A_FULL + buf), 0));
                 if (p.resident && n > 0) continue;
                 for (int s = 0; s < p.tiles_per_group * stages_per_tile; ++s, ++wit) {
                     const uint32_t slot = wit & slot_mask, par = (wit >> slot_log2) & 1u;
                     mbar_wait(bar0 + 8u * (SB_W_FULL + slot), par);
-                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_W_FULL_PEER + slot), 0));
+                    mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_W_FULL + slot), 0));
                 }
             }
         }
