@@ -94,7 +94,8 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
     const uint32_t tmem_base = tmem_base_s;
     const int a_bufs = p.a_bufs;                                      // 1 .. SU_A_BUFS
     const int stages_per_tile = p.n_items * p.n_kb;
-    const uint32_t slot_mask = (uint32_t)p.n_slots - 1u, slot_log2 = (uint32_t)p.slots_log2;   // ring of 4 or 8 weight stages
+    const uint32_t n_slots = (uint32_t)p.n_slots;     // ring of 4 .. 8 weight stages; position = (use << 8) | slot
+    auto ring_next = [n_slots](uint32_t wit) { return ((wit & 0xffu) + 1u == n_slots) ? ((wit & ~0xffu) + 0x100u) : wit + 1u; };
 
     if (warp == 0) {
         // ================= input tile producer =================
@@ -135,8 +136,8 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                 const int ng = v / p.pair_m;
                 for (int tt = 0; tt < p.tiles_per_group; ++tt) {
                     const uint8_t* base = wr + (size_t)(ng * p.tiles_per_group + tt) * p.tile_w_bytes;
-                    for (int s = 0; s < stages_per_tile; ++s, ++wit) {
-                        const uint32_t slot = wit & slot_mask, use = wit >> slot_log2;
+                    for (int s = 0; s < stages_per_tile; ++s, wit = ring_next(wit)) {
+                        const uint32_t slot = wit & 0xffu, use = wit >> 8;
                         if (use > 0) mbar_wait(bar0 + 8u * (SB_W_EMPTY + slot), (use - 1) & 1u);
                         const uint32_t full = bar0 + 8u * (SB_W_FULL + slot);
                         mbar_arrive_expect_tx(full, p.stage_bytes);
@@ -177,8 +178,8 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                         for (int kb = 0; kb < p.n_kb; ++kb, ++s) {
                             uint32_t slot;
                             if (w_wait) {
-                                slot = wit & slot_mask;
-                                const uint32_t par = (wit >> slot_log2) & 1u;
+                                slot = wit & 0xffu;
+                                const uint32_t par = (wit >> 8) & 1u;
                                 mbar_wait_cluster(bar0 + 8u * (SB_W_FULL + slot), par);           // both CTAs' halves
                                 tc_fence_after();
                             } else {
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                             }
                             if (w_wait) {
                                 if (!p.resident) mma_commit<2>(bar0 + 8u * (SB_W_EMPTY + slot));   // slot reusable once these retire
-                                ++wit;
+                                wit = ring_next(wit);
                             }
                         }
                     }
@@ -218,8 +219,8 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
                 mbar_wait(bar0 + 8u * (SB_A_FULL + buf), (uint32_t)(use & 1));
                 mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_A_FULL + buf), 0));
                 if (p.resident && n > 0) continue;
-                for (int s = 0; s < p.tiles_per_group * stages_per_tile; ++s, ++wit) {
-                    const uint32_t slot = wit & slot_mask, par = (wit >> slot_log2) & 1u;
+                for (int s = 0; s < p.tiles_per_group * stages_per_tile; ++s, wit = ring_next(wit)) {
+                    const uint32_t slot = wit & 0xffu, par = (wit >> 8) & 1u;
                     mbar_wait(bar0 + 8u * (SB_W_FULL + slot), par);
                     mbar_arrive_remote(mapa_u32(bar0 + 8u * (SB_W_FULL + slot), 0));
                 }
@@ -516,8 +517,15 @@ int su_plan(SuP& p, const SuLayer& L, int B, int L_in, int n_sms) {
     // 8 KB in flight per SM the L2 -> SM weight stream of ups[1] alone took 119 us (load -> barrier -> relay -> MMA ->
     // commit is a ~1.3 us round trip per stage)
     const uint32_t a_max = ((uint32_t)(128 * L.NB + L.halo_l + L.halo_r) * L.Cin * 2 + 127u) & ~127u;
-    p.n_slots = (!can_reside && a_max + 8u * L.stage_bytes <= SU_SMEM_LIMIT) ? 8 : 4;
-    p.slots_log2 = p.n_slots == 8 ? 3 : 2;
+    p.n_slots = 4;
+    if (!can_reside) {
+        int max_slots = SU_SLOTS;
+#ifdef VO2W_EXPERIMENTS
+        if (getenv("VO2W_SU_SLOTS")) max_slots = std::max(4, std::min(SU_SLOTS, atoi(getenv("VO2W_SU_SLOTS"))));
+#endif
+        while (p.n_slots < max_slots && a_max + (uint32_t)(p.n_slots + 1) * L.stage_bytes <= SU_SMEM_LIMIT) ++p.n_slots;
+    }
+    p.slots_log2 = 0;                        // unused: the ring position carries slot and use count
     const uint32_t ring = (uint32_t)(can_reside ? L.n_tiles * L.n_items * L.n_kb : p.n_slots) * L.stage_bytes;
     int nb_sel = L.NB, bufs_sel = 1;
     {

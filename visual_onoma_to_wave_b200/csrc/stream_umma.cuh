@@ -58,7 +58,7 @@ struct SuP {
     int32_t m_tiles, bm_tiles, pair_m, n_units;
     uint32_t stage_bytes, tile_w_bytes, rank_w_bytes;
     int32_t a_bufs, pf_extra;
-    int32_t n_slots, slots_log2;   // weight ring stages in use (4 or 8)
+    int32_t n_slots, slots_log2;   // weight ring stages in use (4 .. 8; slots_log2 unused)
     uint32_t a_off[SU_A_BUFS], ring_off, smem_bytes;
     int32_t resident;          // the weights of a unit fit the ring and every unit uses the same ones: loaded once
     int32_t dbg;               // what-if timing switches, only settable in -DVO2W_EXPERIMENTS builds (results are wrong)
