@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         // ncu source page showed a third of e2's stall samples as instruction fetch (stall_no_inst) -- in launches
         // where e2 is the busiest role (C <= 64).  Addresses are computed per chunk instead.
         constexpr int ITEMS = NB * GROUPS / 2;           // per warp
-        constexpr int JU = ITEMS > 2 ? ITEMS : 1;        // generic drain: flat where e2 is on the critical path between tiles (ND = 1)
+        constexpr int JU = ITEMS > 2 ? 2 * ITEMS : 1;    // generic drain: flat where e2 is on the critical path between tiles (ND = 1)
         const int q4 = warp & 3;
         const int q = q4 * 32 + lane;
         const int half = warp >> 2;
@@ -600,11 +600,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
         const int back = 2 * p.h2max;
         float* const part = reinterpret_cast<float*>(smem + p.part_off);   // POST: [2][PAIR_POST_K][PAIR_POST_ROWS] partial sums
         long long c_wait = 0, c_work = 0;
-        // Generic drain (MRF launches, conv_post on board): the residual rows of the segments of ONE item live in R, and
-        // are fetched one use ahead -- the registers are refilled with the next item's rows (the next tile's first item
-        // after the last) right after their last use, so the L2 round trip runs under the rest of the item.  With the loads
-        // issued at the top of a tile e2 waited ~1000 cycles per tile for them (ncu source page).
-        uint4 R[PAIR_MAX_SEG][4];                        // [segment][chunk] of the current item
+        // Generic drain (MRF launches, conv_post on board), in 16-column half-items: cc = half (cc & 1) of item cc >> 1.  The
+        // residual rows of the segments of ONE half-item live in R and are fetched one use ahead -- the registers are
+        // refilled with the next half-item's rows (the next tile's first after the last) right after their last use, so
+        // the L2 round trip runs under the rest of the half-item.  With the loads issued at the top of a tile e2 waited
+        // ~1000 cycles per tile for them (ncu source page).
+        uint4 R[PAIR_MAX_SEG][2];                        // [segment][chunk] of the current half-item
         auto item_geom = [&](const TileCoord& t, int j, int& blk, int& g, int& rel, bool& ok) {
             const int i = half + 2 * j;
             blk = i / GROUPS;
@@ -612,21 +613,16 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             rel = blk == 0 ? 0 : blk * 128 - back;
             ok = t.live && (t.l0 + rel + q) < p.L && (blk > 0 || q < 128 - back) && !(p.dbg & 1);
         };
-        auto load_res = [&](const TileCoord& t, int j, int hh) {   // half hh (16 columns) of item j, all segments, into R[s][2 hh ..]
+        auto load_res = [&](const TileCoord& t, int cc) {   // half-item cc, all segments, into R[s]
             int blk, g, rel; bool ok;
-            item_geom(t, j, blk, g, rel, ok);
+            item_geom(t, cc >> 1, blk, g, rel, ok);
             if (!ok) return;
-            const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4 + hh * 2) * e_step;
+            const size_t e = ((size_t)t.b * CHUNKS * p.Lp + VO2W_PAD_ROWS + t.l0 + q) * 8 + (size_t)rel * 8 + (size_t)(g * 4 + (cc & 1) * 2) * e_step;
 #pragma unroll
             for (int s = 0; s < PAIR_MAX_SEG; ++s)
                 if (s < n_seg) {
-                    if (hh == 0) {
-                        R[s][0] = __ldg((const uint4*)(p.seg[s].xa + e));
-                        R[s][1] = __ldg((const uint4*)(p.seg[s].xa + e + e_step));
-                    } else {
-                        R[s][2] = __ldg((const uint4*)(p.seg[s].xa + e));
-                        R[s][3] = __ldg((const uint4*)(p.seg[s].xa + e + e_step));
-                    }
+                    R[s][0] = __ldg((const uint4*)(p.seg[s].xa + e));
+                    R[s][1] = __ldg((const uint4*)(p.seg[s].xa + e + e_step));
                 }
         };
         // Residual by initialisation (p.rinit: single-segment launches).  y = x + conv2(...): instead of fetching x again
@@ -676,9 +672,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             for (int u = 0; u < ND && u < p.iters; ++u) init_d2(u);
         } else if (p.iters > 0) {
             griddep_wait();                              // the residual rows are read straight from the previous launch's output
-            const TileCoord t0 = tile_of(p, 0);
-            load_res(t0, 0, 0);
-            load_res(t0, 0, 1);
+            load_res(tile_of(p, 0), 0);
         }
         for (int it = 0; it < p.iters; ++it) {
             if (warp == 0) trace(p, 7, it * n_seg + n_seg - 1, 0);
@@ -741,71 +735,73 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
             } else {
                 const TileCoord tn = tile_of(p, has_next ? it + 1 : it);
 #pragma unroll JU
-                for (int j = 0; j < ITEMS; ++j) {
+                for (int cc = 0; cc < 2 * ITEMS; ++cc) {
+                    // 16 live accumulator registers next to the 24 of R: with a 32-column load and a whole item's residuals
+                    // in registers this path spilled, and the spills were reloaded in every loop of the kernel
                     int blk, g, rel; bool ok;
-                    item_geom(t, j, blk, g, rel, ok);
-                    // An item is drained in two halves of 16 columns: 16 live accumulator registers next to the 48 of R
-                    // (with a 32-column load this path spilled, and the spills were reloaded in every loop of the kernel).
+                    item_geom(t, cc >> 1, blk, g, rel, ok);
+                    const int hh = cc & 1;
+                    uint32_t r[16];
+                    tmem_ld16(d2n + (uint32_t)(blk * C + g * 32 + hh * 16), r);
+                    tmem_ld_wait();
+                    float v[16];
 #pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        uint32_t r[16];
-                        tmem_ld16(d2n + (uint32_t)(blk * C + g * 32 + hh * 16), r);
-                        tmem_ld_wait();
-                        float v[16];
+                    for (int c = 0; c < 16; ++c) v[c] = __uint_as_float(r[c]);
+                    // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
+                    auto add_res = [&](const uint4& x0, const uint4& x1) {
+                        const uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
 #pragma unroll
-                        for (int c = 0; c < 16; ++c) v[c] = __uint_as_float(r[c]);
-                        // the stream holds s = bf16(leaky_relu(x, 0.1)); the residual is x = s >= 0 ? s : 10 s  (exact in fp32)
-                        auto add_res = [&](const uint4& x0, const uint4& x1) {
-                            const uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const float2 f = unpack_bf16x2(w[i]);
-                                v[2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[2 * i] + f.x);
-                                v[2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[2 * i + 1] + f.y);
-                            }
-                        };
-                        if (ok) {
-#pragma unroll
-                            for (int s = 0; s < PAIR_MAX_SEG; ++s)
-                                if (s < n_seg) add_res(R[s][2 * hh], R[s][2 * hh + 1]);
+                        for (int i = 0; i < 8; ++i) {
+                            const float2 f = unpack_bf16x2(w[i]);
+                            v[2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[2 * i] + f.x);
+                            v[2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[2 * i + 1] + f.y);
                         }
-                        // the registers are free again: fetch what uses them next (the same half of the next item, or of
-                        // the next tile's first item) while this half is scaled and stored
-                        if (j + 1 < ITEMS) load_res(t, j + 1, hh);
-                        else if (has_next) load_res(tn, 0, hh);
-                        if (ok) {
-                            // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
+                    };
+                    if (ok) {
 #pragma unroll
-                            for (int c = 0; c < 16; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
-                        }
-                        if constexpr (POST) {
-                            // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
-                            // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
-                            // parameters: constant-bank operands of the FFMAs) and leaves 7 partial sums in shared memory
-                            // (the second half adds to the first's); the taps are summed across rows after the tile's
-                            // barrier.  Rows outside the utterance are conv_post's zero padding.  x is never written to HBM.
-                            if (blk > 0 || q < 128 - back) {
-                                float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
+                        for (int s = 0; s < PAIR_MAX_SEG; ++s)
+                            if (s < n_seg) add_res(R[s][0], R[s][1]);
+                    }
+                    // the registers are free again: fetch what uses them next while this half-item is scaled and stored
+                    if (cc + 1 < 2 * ITEMS) load_res(t, cc + 1);
+                    else if (has_next) load_res(tn, 0);
+                    if (ok) {
+                        // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
-                                for (int jj = 0; jj < PAIR_POST_K; ++jj) {
-                                    float a = hh == 0 ? 0.f : pr[jj * PAIR_POST_ROWS];
-                                    if (ok) {
+                        for (int c = 0; c < 16; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
+                    }
+                    if constexpr (POST) {
+                        // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
+                        // in fp32 registers, so each thread reduces its row against the 7 taps (weights are kernel
+                        // parameters: constant-bank operands of the FFMAs; the 7 sums advance together, so no FFMA waits
+                        // for the one before it) and leaves 7 partial sums in shared memory (the second half adds to the
+                        // first's); the taps are summed across rows after the tile's barrier.  Rows outside the utterance
+                        // are conv_post's zero padding.  x is never written to HBM.
+                        if (blk > 0 || q < 128 - back) {
+                            float* pr = part + (it & 1) * (PAIR_POST_K * PAIR_POST_ROWS) + rel + q;
+                            float a[PAIR_POST_K];
 #pragma unroll
-                                        for (int c = 0; c < 16; ++c) a = fmaf(v[c], p.post_w[jj * 32 + hh * 16 + c], a);
-                                    }
-                                    pr[jj * PAIR_POST_ROWS] = a;
+                            for (int jj = 0; jj < PAIR_POST_K; ++jj) a[jj] = hh == 0 ? 0.f : pr[jj * PAIR_POST_ROWS];
+                            if (ok) {
+                                const float* pw = p.post_w + hh * 16;
+#pragma unroll
+                                for (int c = 0; c < 16; ++c) {
+#pragma unroll
+                                    for (int jj = 0; jj < PAIR_POST_K; ++jj) a[jj] = fmaf(v[c], pw[jj * 32 + c], a[jj]);
                                 }
                             }
-                        } else if (ok) {
-                            const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4 + hh * 2) * e_step;
-                            // out = bf16(...), one rounding
 #pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                uint4 o;
-                                o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
-                                o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
-                                *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
-                            }
+                            for (int jj = 0; jj < PAIR_POST_K; ++jj) pr[jj * PAIR_POST_ROWS] = a[jj];
+                        }
+                    } else if (ok) {
+                        const size_t e = e_tile + (size_t)rel * 8 + (size_t)(g * 4 + hh * 2) * e_step;
+                        // out = bf16(...), one rounding
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[h * 8 + 0], v[h * 8 + 1]); o.y = pack_bf16x2(v[h * 8 + 2], v[h * 8 + 3]);
+                            o.z = pack_bf16x2(v[h * 8 + 4], v[h * 8 + 5]); o.w = pack_bf16x2(v[h * 8 + 6], v[h * 8 + 7]);
+                            *(uint4*)(p.out_act + e + (size_t)h * e_step) = o;
                         }
                     }
                 }
