@@ -248,3 +248,30 @@ def test_back_to_back_forwards_are_bit_identical(dev, gens):
         side.synchronize()
         for o in o2:
             assert torch.equal(o, refs[0]), precision
+
+
+def test_fresh_workspace_on_dirty_memory(dev, gens):
+    """A workspace that has not run a (B, T) before only gets the pad / tail rows of its operand buffers cleared (one launch;
+    csrc/generator.cu zero_pad_rows), not the whole allocation.  Here the allocator is made to hand out memory full of NaN
+    bit patterns (0xFF bytes) for a shape the generator has not seen: the result must equal the one computed on a
+    zero-filled allocation of the same shape, bit for bit -- anything that read a row nobody wrote would be NaN."""
+    gen, sd = gens
+    for B, T in ((3, 37), (2, 130)):
+        mel = synthetic_mel(B, T, seed=31).to(dev)
+        g0 = make_gen(sd, "bf16", dev)
+        torch.cuda.empty_cache()
+        need = _lib.lib().vo2w_generator_workspace_bytes(g0._get_handle(dev), B, T)
+        clean = torch.zeros(need + (64 << 20), dtype=torch.uint8, device=dev)
+        del clean                                           # cached block, all zero: the workspace is carved from it
+        ref = g0(mel).clone()
+        assert bool(torch.isfinite(ref).all())
+        del g0
+        torch.cuda.empty_cache()
+        g1 = make_gen(sd, "bf16", dev)
+        dirty = torch.full((need + (64 << 20),), 0xFF, dtype=torch.uint8, device=dev)
+        del dirty                                           # cached block of NaN patterns
+        got = g1(mel)
+        assert torch.equal(got, ref), (B, T)
+        got16 = g1.infer_host(mel.cpu(), int16_scale=32768.0)   # the host int16 path on the same (now used) workspace
+        assert torch.equal(got16, torch.from_numpy((ref.squeeze(1).cpu().numpy() * np.float32(32768.0)).astype("int16")))
+        del g1

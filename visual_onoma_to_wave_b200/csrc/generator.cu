@@ -417,6 +417,54 @@ extern "C" int vo2w_generator_get_timing(vo2w_generator* g, float* ms, int32_t* 
 // ---------------------------------------------------------------------------------------
 namespace {
 
+// The bf16 kernels write rows [0, L) of an operand buffer [B][C/8][Lp][8] and rely on every other row -- the 32 pad rows
+// in front, everything behind sample L -- reading as zero (= the convolutions' zero padding).  On a workspace that has not
+// run this (B, T) before, those rows are cleared by ONE launch over all 34 buffers (~0.3 % of the workspace; clearing the
+// whole workspace cost 0.6 ms of HBM time at B = 128 whenever a serving loop changed its batch shape).
+#define ZP_MAX_BUFS 40
+struct ZeroPads {
+    int n;
+    unsigned long long off[ZP_MAX_BUFS];     // byte offset of the buffer inside the workspace
+    int segs[ZP_MAX_BUFS];                   // B * C / 8 segments of Lp rows
+    int L[ZP_MAX_BUFS], Lp[ZP_MAX_BUFS];
+};
+
+__global__ void __launch_bounds__(256) zero_pad_rows_kernel(uint8_t* ws, const __grid_constant__ ZeroPads z) {
+    const int buf = blockIdx.y;
+    if (buf >= z.n) return;
+    const int L = z.L[buf], Lp = z.Lp[buf], tail0 = VO2W_PAD_ROWS + L, n_pad = VO2W_PAD_ROWS + (Lp - tail0);
+    uint4* base = reinterpret_cast<uint4*>(ws + z.off[buf]);
+    const long long total = (long long)z.segs[buf] * n_pad;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        const long long seg = i / n_pad;
+        const int r = (int)(i - seg * n_pad);
+        const int row = r < VO2W_PAD_ROWS ? r : tail0 + (r - VO2W_PAD_ROWS);
+        base[seg * Lp + row] = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+int zero_pad_rows(const vo2w_generator* g, const Plan& p, void* workspace, cudaStream_t st) {
+    ZeroPads z;
+    z.n = 0;
+    auto add = [&](size_t off, int C, long long L, long long Lp) {
+        z.off[z.n] = off; z.segs[z.n] = p.B * (C / 8); z.L[z.n] = (int)L; z.Lp[z.n] = (int)Lp;
+        ++z.n;
+    };
+    add(p.melb, 80, p.T, vo2w_padded_len(p.T));
+    add(p.a0, g->cfg.upsample_initial_channel, p.T, vo2w_padded_len(p.T));
+    for (int i = 0; i < g->n_stage; ++i) {
+        const StageBufs& s = p.st[i];
+        add(s.xa, s.C, s.L, s.Lp);
+        for (int j = 0; j < g->nk; ++j)
+            for (int m = 0; m < 2; ++m) add(s.ra[j][m], s.C, s.L, s.Lp);
+        add(s.mrf, s.C, s.L, s.Lp);
+    }
+    VO2W_REQUIRE(z.n <= ZP_MAX_BUFS, "zero_pad_rows: %d buffers", z.n);
+    zero_pad_rows_kernel<<<dim3(64, (unsigned)z.n), 256, 0, st>>>((uint8_t*)workspace, z);
+    VO2W_CUDA_OK(cudaGetLastError());
+    return VO2W_OK;
+}
+
 // kind: 0 = layout / conversion helper, 1 = single convolution (umma_conv_kernel / fp32 kernels), 2 = fused ResBlock iterations
 int mark_launch(vo2w_generator* g, int kind, cudaStream_t st) {
     ++g->last_launches;
@@ -623,9 +671,9 @@ static int forward_impl(vo2w_generator* g, const float* mel, int B, int T, float
         }
         VO2W_CUDA_OK(cudaEventRecord(g->ev[0], st));
     }
-    if (ws_fresh && g->precision == VO2W_PREC_BF16)   // halo / tail rows of the operand buffers must read as zero
-        VO2W_CUDA_OK(cudaMemsetAsync(workspace, 0, p.total, st));
     int rc;
+    if (ws_fresh && g->precision == VO2W_PREC_BF16)   // pad / tail rows of the operand buffers must read as zero
+        if ((rc = zero_pad_rows(g, p, workspace, st)) != VO2W_OK) return rc;
     if (g->precision == VO2W_PREC_BF16) {
         rc = forward_bf16(g, p, mel, wav, wav_i16, i16_scale, (uint8_t*)workspace, st);
         if (rc != VO2W_OK || g->last_fused_post) return rc;
