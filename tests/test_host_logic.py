@@ -100,3 +100,18 @@ def test_round_durations_matches_golden(golden_dir):
     g = np.load(os.path.join(golden_dir, "length_regulator.npz"))
     got = v.round_durations(torch.from_numpy(g["round.logd"]), 1.5)
     np.testing.assert_array_equal(got.numpy(), g["round.dur"])
+
+
+def test_pipeline_chunks_cover_the_batch_in_order():
+    """hifigan.pipeline_chunks: the sub-batches of one host call tile [0, B) in order, none larger than the sub-batch, and
+    for a long job the first and the last ones are the small ones (their copies are what the pipeline cannot hide)."""
+    from visual_onoma_to_wave_b200.hifigan import pipeline_chunks
+    for B in list(range(1, 70)) + [127, 128, 129, 255, 256, 300, 1000, 1024, 4096]:
+        for sub in (1, 2, 3, 16, 63, 64, 128):
+            ch = pipeline_chunks(B, sub)
+            assert ch[0][0] == 0 and ch[-1][1] == B
+            assert all(a[1] == b[0] for a, b in zip(ch, ch[1:]))
+            assert all(0 < e - s <= sub for s, e in ch)
+    sizes = [e - s for s, e in pipeline_chunks(1024, 128)]
+    assert sizes[0] == 32 and sizes[-1] <= 32 and sizes.count(128) == 7 and sum(sizes) == 1024
+    assert [e - s for s, e in pipeline_chunks(7, 3)] == [3, 3, 1]          # small sub-batches: plain walk

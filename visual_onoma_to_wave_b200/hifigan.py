@@ -115,6 +115,36 @@ def _host_copy(dst: torch.Tensor, src: torch.Tensor, workers: int = 4) -> None:
         f.result()
 
 
+def pipeline_chunks(B: int, sub: int):
+    """(start, end) of the sub-batches one host call walks.  Full sub-batches in the middle; the first one and the last
+    ones are smaller (down to a quarter, from sub-batches of 64 up): what the two-stream pipeline cannot hide is the
+    host->device copy in front of the first forward and the device->host copy behind the last one, and both are
+    proportional to their sub-batch (at 8 ranks on one host the last copy of 23 MB per rank was 3 % of the step).  A
+    batch-shape change costs one small launch (zero_pad_rows), and a forward is linear in its batch down to 32."""
+    if B <= sub or sub < 64:
+        return [(a, min(a + sub, B)) for a in range(0, B, sub)]
+    small = sub // 4
+    sizes = [small]
+    left = B - small
+    while left > sub:
+        sizes.append(sub)
+        left -= sub
+    while left > 2 * small:                         # taper: half of what is left, ..., then two pieces of about `small`
+        sizes.append(left // 2)
+        left -= left // 2
+    if left > small:
+        sizes.append(left - left // 2)
+        left //= 2
+    if left:
+        sizes.append(left)
+    out, a = [], 0
+    for n in sizes:
+        out.append((a, a + n))
+        a += n
+    assert a == B and all(0 < e - b <= sub for b, e in out)
+    return out
+
+
 class Generator(nn.Module):
     """HiFi-GAN generator, mel [B,80,T] -> wav [B,1,T*prod(upsample_rates)] (models.py:112-174).
 
@@ -284,8 +314,7 @@ class Generator(nn.Module):
                         _host_copy(out[a:b], sl["pin"][: b - a])  # host copy; the other stream's kernels keep running
                     sl["pending"] = None
 
-            for i, a in enumerate(range(0, B, sub)):
-                b = min(a + sub, B)
+            for i, (a, b) in enumerate(pipeline_chunks(B, sub)):
                 sl = slots[i & 1]
                 retire(sl)
                 fresh = sl["shape"] != (b - a, T)            # the workspace layout depends on the batch size
