@@ -261,7 +261,12 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL as the contract says; VO2W_BENCH_PG=gloo (experiments: the path has no data-path collective, the group only
+        # carries the timing barrier and the max over ranks) keeps NCCL out of the process
+        if os.environ.get("VO2W_BENCH_PG", "nccl") == "gloo":
+            dist.init_process_group("gloo")
+        else:
+            dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
     cfg_m = {"vocoder": {"model": "HiFi-GAN"}}
     mel_all = synthetic_mel(N_UTT, T_FRAMES, seed=0)
@@ -286,7 +291,7 @@ def run_ours(args):
         barrier()
         wall = time.perf_counter() - t0
         clocks = sampler.stop() if sampler else None
-        ms = max_over_ranks([e0.elapsed_time(e1), wall * 1e3], dev)      # the job's time is its slowest rank's
+        ms = max_over_ranks([e0.elapsed_time(e1), wall * 1e3], None if os.environ.get("VO2W_BENCH_PG") == "gloo" else dev)      # the job's time is its slowest rank's
         return ms[0], ms[1], clocks
 
     def run_job(gen, n_job, sub_batch, steps, warm, sampler=None):

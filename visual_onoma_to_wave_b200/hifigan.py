@@ -316,7 +316,12 @@ class Generator(nn.Module):
 
             for i, (a, b) in enumerate(pipeline_chunks(B, sub)):
                 sl = slots[i & 1]
-                retire(sl)
+                # Results copied straight into the caller's buffer need no host step between sub-batches: a slot's
+                # workspace / staging tensors are reused in stream order, so the whole call is queued at once and the GPU
+                # never waits for the host to notice a finished sub-batch (both slots used to finish together, and the
+                # next H2D + 34 launches then started from an idle GPU).  With pinned staging the host copy comes first.
+                if not direct:
+                    retire(sl)
                 fresh = sl["shape"] != (b - a, T)            # the workspace layout depends on the batch size
                 sl["shape"] = (b - a, T)
                 src = mel_host[a:b]
