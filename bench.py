@@ -277,6 +277,10 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def timed(fn, steps, warmup, sampler=None):
+        # A barrier BEFORE the warm-up as well: the first collective on an NCCL communicator sets its connections up
+        # (hundreds of ms with the GPU idle).  Left between warm-up and timing it hands the timed steps a cold, power-
+        # credited GPU: measured at 2 ranks, 3 steps: 102.6 ms per step instead of the steady 107.8.
+        barrier()
         for _ in range(warmup):
             fn()
         barrier()
