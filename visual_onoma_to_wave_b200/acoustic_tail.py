@@ -34,9 +34,13 @@ class AcousticTail(nn.Module):
         has: (output, postnet_output, e_predictions, k_predictions, log_d_predictions, d_rounded, mel_masks, mel_lens)."""
         if self.training:
             raise RuntimeError("AcousticTail: the B200 path is inference only (call .eval())")
-        (output, e_predictions, k_predictions, log_d_predictions, d_rounded, mel_lens, mel_masks) = self.variance_adaptor(
-            encoder_output, src_masks, mel_masks, max_mel_len, e_targets, k_targets, d_targets, e_control, d_control)
-        output, mel_masks = self.decoder(output, mel_masks)
-        output = mel_linear(output, self.mel_linear.weight, self.mel_linear.bias)
-        postnet_output = self.postnet(output, add_input=True)        # postnet(output) + output, one pass
+        nvtx = torch.cuda.nvtx.range             # a no-op unless a profiler is attached
+        with nvtx("vo2w.variance_adaptor"):
+            (output, e_predictions, k_predictions, log_d_predictions, d_rounded, mel_lens, mel_masks) = self.variance_adaptor(
+                encoder_output, src_masks, mel_masks, max_mel_len, e_targets, k_targets, d_targets, e_control, d_control)
+        with nvtx("vo2w.decoder"):
+            output, mel_masks = self.decoder(output, mel_masks)
+        with nvtx("vo2w.mel_linear_postnet"):
+            output = mel_linear(output, self.mel_linear.weight, self.mel_linear.bias)
+            postnet_output = self.postnet(output, add_input=True)        # postnet(output) + output, one pass
         return (output, postnet_output, e_predictions, k_predictions, log_d_predictions, d_rounded, mel_masks, mel_lens)

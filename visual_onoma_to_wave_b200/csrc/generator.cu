@@ -13,6 +13,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "conv_simt.cuh"
 #include "conv_tf32.cuh"
 #include "rows.cuh"
@@ -482,6 +484,16 @@ int mark_launch(vo2w_generator* g, int kind, cudaStream_t st) {
 #define VO2W_RUNK(kind, expr) do { int _rc = (expr); if (_rc != VO2W_OK) return _rc; _rc = mark_launch(g, kind, st); if (_rc != VO2W_OK) return _rc; } while (0)
 #define VO2W_RUN(expr) VO2W_RUNK(1, expr)
 
+// NVTX ranges (header-only nvtx3: a no-op costing a function-pointer check unless a profiler is attached) around a forward
+// and its stages, so that `ncu --nvtx --nvtx-include "vo2w.stage2/"` or a timeline tool can pick a stage out of the 34 launches.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+static const char* const kStageRange[4] = {"vo2w.stage0", "vo2w.stage1", "vo2w.stage2", "vo2w.stage3"};
+
 // Generator.forward (models.py:149-165) on the tcgen05 path.
 int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav, short* wav_i16, float i16_scale, uint8_t* ws,
                  cudaStream_t st) {
@@ -493,6 +505,7 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
     // mel [B,80,T] fp32 -> operand buffer
     VO2W_RUNK(0, pack_ncl_to_operand(mel, bf(p.melb), B, 80, T, (int)vo2w_padded_len(T), 1.0f, st));
     {   // x = conv_pre(mel); the only consumer is leaky_relu(0.1) -> ups[0]
+        NvtxRange r("vo2w.conv_pre");
         if (g->use_stream) {
             VO2W_RUN(su_launch(g->s_pre, bf(p.melb), bf(p.a0), nullptr, 0.1f, B, T, st));
         } else {
@@ -508,6 +521,7 @@ int forward_bf16(vo2w_generator* g, const Plan& p, const float* mel, float* wav,
     long long L_in = T;
     for (int i = 0; i < g->n_stage; ++i) {
         const StageBufs& s = p.st[i];
+        NvtxRange r(kStageRange[i & 3]);                 // ups[i] + the stage's three ResBlocks + MRF (+ conv_post)
         if (g->use_stream) {   // x = ups[i](leaky_relu(x)): polyphase implicit GEMM on persistent CTA pairs
             VO2W_RUN(su_launch(g->s_ups[i], stage_in, bf(s.xa), nullptr, 0.1f, B, (int)L_in, st));
         } else {
@@ -652,6 +666,7 @@ static int forward_impl(vo2w_generator* g, const float* mel, int B, int T, float
     VO2W_REQUIRE(g && mel && wav, "generator_forward: null argument");
     VO2W_REQUIRE(B > 0 && T > 0, "generator_forward: empty batch (B=%d T=%d)", B, T);
     VO2W_REQUIRE(B <= 65535, "generator_forward: batch %d exceeds grid.z", B);
+    NvtxRange range(g->precision == VO2W_PREC_BF16 ? "vo2w.generator.forward.bf16" : "vo2w.generator.forward.fp32");
     const Plan p = make_plan(g, B, T);
     if (workspace_bytes < p.total || !workspace) {
         vo2w_set_error("generator_forward: workspace %zu bytes, need %zu", workspace_bytes, p.total);

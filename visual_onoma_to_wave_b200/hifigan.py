@@ -322,6 +322,7 @@ class Generator(nn.Module):
                 # next H2D + 34 launches then started from an idle GPU).  With pinned staging the host copy comes first.
                 if not direct:
                     retire(sl)
+                torch.cuda.nvtx.range_push(f"vo2w.sub_batch[{a}:{b}]")
                 fresh = sl["shape"] != (b - a, T)            # the workspace layout depends on the batch size
                 sl["shape"] = (b - a, T)
                 src = mel_host[a:b]
@@ -335,6 +336,7 @@ class Generator(nn.Module):
                            "vo2w_generator_forward_host_async")
                 launches += lib.vo2w_generator_last_launches(handle)
                 sl["pending"] = (a, b)
+                torch.cuda.nvtx.range_pop()
             for sl in slots:
                 retire(sl)
             self.last_launches = launches
