@@ -652,8 +652,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
 #pragma unroll
                     for (int k2 = 0; k2 < 4; ++k2) {      // x = s >= 0 ? s : 10 s, exact in fp32
                         const float2 f = unpack_bf16x2(w[k2]);
-                        r[h * 8 + 2 * k2] = __float_as_uint(fmaf(fminf(f.x, 0.f), 9.f, f.x));
-                        r[h * 8 + 2 * k2 + 1] = __float_as_uint(fmaf(fminf(f.y, 0.f), 9.f, f.y));
+                        float x0, x1;
+                        fma2(x0, x1, fminf(f.x, 0.f), fminf(f.y, 0.f), 9.f, f.x, f.y);
+                        r[h * 8 + 2 * k2] = __float_as_uint(x0);
+                        r[h * 8 + 2 * k2 + 1] = __float_as_uint(x1);
                     }
                 }
                 tmem_st16(d2u + (uint32_t)(blk * C + hc * 8), r);
@@ -700,7 +702,14 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 auto store_chunk = [&](const uint32_t (&r)[16], size_t e) {
                     float v[16];
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) v[c] = fmaxf(__uint_as_float(r[c]) * s_pos, __uint_as_float(r[c]) * s_neg);
+                    for (int c = 0; c < 16; c += 2) {
+                        const float y0 = __uint_as_float(r[c]), y1 = __uint_as_float(r[c + 1]);
+                        float a0, a1, n0, n1;
+                        mul2(a0, a1, y0, y1, s_pos);
+                        mul2(n0, n1, y0, y1, s_neg);
+                        v[c] = fmaxf(a0, n0);
+                        v[c + 1] = fmaxf(a1, n1);
+                    }
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         uint4 o;
@@ -753,8 +762,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const float2 f = unpack_bf16x2(w[i]);
-                            v[2 * i] = fmaf(fminf(f.x, 0.f), 9.f, v[2 * i] + f.x);
-                            v[2 * i + 1] = fmaf(fminf(f.y, 0.f), 9.f, v[2 * i + 1] + f.y);
+                            float t0, t1;
+                            add2(t0, t1, v[2 * i], v[2 * i + 1], f.x, f.y);
+                            fma2(v[2 * i], v[2 * i + 1], fminf(f.x, 0.f), fminf(f.y, 0.f), 9.f, t0, t1);
                         }
                     };
                     if (ok) {
@@ -768,7 +778,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                     if (ok) {
                         // leaky_relu(v * scale, out_slope); max(a, a * slope) for slope < 1
 #pragma unroll
-                        for (int c = 0; c < 16; ++c) v[c] = fmaxf(v[c] * s_pos, v[c] * s_neg);
+                        for (int c = 0; c < 16; c += 2) {
+                            float a0, a1, n0, n1;
+                            mul2(a0, a1, v[c], v[c + 1], s_pos);
+                            mul2(n0, n1, v[c], v[c + 1], s_neg);
+                            v[c] = fmaxf(a0, n0);
+                            v[c + 1] = fmaxf(a1, n1);
+                        }
                     }
                     if constexpr (POST) {
                         // conv_post + tanh (models.py:161-163) ride this launch: the row is leaky_relu(xs / num_kernels, 0.01)
