@@ -242,17 +242,25 @@ __global__ void __launch_bounds__(SU_THREADS, 1) stream_umma_kernel(const __grid
         // bias + leaky-relu + bf16: 32 columns -> 4 x 16 bytes
         auto convert = [&](const uint32_t (&r)[32], const float* bias, uint4 (&w)[4], float (&v)[32]) {
 #pragma unroll
-            for (int c = 0; c < 32; c += 4) {
+            for (int c = 0; c < 32; c += 4) {     // packed fp32 (FADD2 / FMUL2): two IEEE operations per issue slot
                 const float4 bv = __ldg((const float4*)(bias + c));
-                v[c] = __uint_as_float(r[c]) + bv.x; v[c + 1] = __uint_as_float(r[c + 1]) + bv.y;
-                v[c + 2] = __uint_as_float(r[c + 2]) + bv.z; v[c + 3] = __uint_as_float(r[c + 3]) + bv.w;
+                add2(v[c], v[c + 1], __uint_as_float(r[c]), __uint_as_float(r[c + 1]), bv.x, bv.y);
+                add2(v[c + 2], v[c + 3], __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), bv.z, bv.w);
+            }
+            float a[32];                          // leaky_relu(v, slope) = max(v, v * slope) for 0 <= slope <= 1 (su_launch checks)
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+                float n0, n1;
+                mul2(n0, n1, v[c], v[c + 1], p.out_slope);
+                a[c] = fmaxf(v[c], n0);
+                a[c + 1] = fmaxf(v[c + 1], n1);
             }
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
-                w[h].x = pack_bf16x2(lrelu(v[8 * h + 0], p.out_slope), lrelu(v[8 * h + 1], p.out_slope));
-                w[h].y = pack_bf16x2(lrelu(v[8 * h + 2], p.out_slope), lrelu(v[8 * h + 3], p.out_slope));
-                w[h].z = pack_bf16x2(lrelu(v[8 * h + 4], p.out_slope), lrelu(v[8 * h + 5], p.out_slope));
-                w[h].w = pack_bf16x2(lrelu(v[8 * h + 6], p.out_slope), lrelu(v[8 * h + 7], p.out_slope));
+                w[h].x = pack_bf16x2(a[8 * h + 0], a[8 * h + 1]);
+                w[h].y = pack_bf16x2(a[8 * h + 2], a[8 * h + 3]);
+                w[h].z = pack_bf16x2(a[8 * h + 4], a[8 * h + 5]);
+                w[h].w = pack_bf16x2(a[8 * h + 6], a[8 * h + 7]);
             }
         };
         auto store_f32 = [&](const float (&v)[32], int b, int co, long long orow) {
@@ -598,6 +606,7 @@ int su_plan(SuP& p, const SuLayer& L, int B, int L_in, int n_sms) {
 int su_launch(const SuLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out, float* out_f32, float out_slope, int B, int L_in,
               cudaStream_t st) {
     VO2W_REQUIRE(L.w_dev && L.bias_dev && in && (out || out_f32), "stream conv: layer not uploaded or null buffer");
+    VO2W_REQUIRE(out_slope >= 0.f && out_slope <= 1.f, "stream conv: output slope %f outside [0, 1]", out_slope);
     static bool attr_set[VO2W_MAX_DEV];
     const int cur = vo2w_cur_dev();
     if (!attr_set[cur]) {
