@@ -360,7 +360,8 @@ def run_ours(args):
 
     # roofline of the dominant kernel, pair_umma_kernel (28 of the 34 launches of a forward): its launches are timed
     # live with CUDA events on the launching stream (vo2w_generator_set_timing), one sub-batch per pass, right after
-    # the timed steps (GPU hot).  achieved = algorithmic FLOPs of those launches / their summed duration.
+    # the timed steps (GPU hot).  achieved = algorithmic FLOPs of the kernel's launches in a step / (the step's device
+    # time x the kernel's share of a forward); the event pass's own, serialised durations are reported next to it.
     a, b = chunks[0]
     pair_ms, all_ms, n_pair = 0.0, 0.0, 0
     passes = 3
@@ -374,10 +375,24 @@ def run_ours(args):
             for m, k in zip(ms_l, kinds):
                 kind_ms[k] = kind_ms.get(k, 0.0) + m
     if n_pair:
+        # One event per launch serialises the launches (an event between two kernels is a full dependency: no programmatic
+        # dependent launch, every kernel's tail and set-up exposed), so the per-launch durations of this pass are ~5 - 9 %
+        # longer than the same launches inside the timed steps.  What the pass gives reliably is the kernel's SHARE of a
+        # forward (it agrees with the ncu launch list, profiles/r02_bench_launches.csv); the kernel's time inside the timed
+        # region is that share of the region's device time.  Both figures are reported.
         flops_pair = PAIR_FLOP_PER_FRAME * (b - a) * T_FRAMES * passes
-        achieved = flops_pair / (pair_ms * 1e-3) / 1e12
-        per_launch = {"flops_per_launch": flops_pair / n_pair, "avg_launch_us": pair_ms * 1e3 / n_pair,
-                      "share_of_forward_time": pair_ms / all_ms, "launches_timed": n_pair,
+        share = pair_ms / all_ms
+        serialised = flops_pair / (pair_ms * 1e-3) / 1e12
+        launches_in_step = (n_pair // passes) * len(chunks)
+        pair_ms_in_step = ms_per_step * share
+        achieved = PAIR_FLOP_PER_FRAME * n_local * T_FRAMES / (pair_ms_in_step * 1e-3) / 1e12
+        per_launch = {"flops_per_launch": flops_pair / n_pair, "avg_launch_us": pair_ms_in_step * 1e3 / launches_in_step,
+                      "how": "CUDA events around the timed steps (ms_per_step) x the kernel's share of a forward, measured with one "
+                             "CUDA event per launch on the launching stream right after the timed steps",
+                      "serialised": {"avg_launch_us": pair_ms * 1e3 / n_pair, "achieved": serialised,
+                                     "frac": serialised / peaks["bf16_tflops_sustained"],
+                                     "what": "the per-launch event pass itself: launches serialised by the events between them"},
+                      "share_of_forward_time": share, "launches_timed": n_pair,
                       "other_launches": {"single_conv_share_of_forward_time": kind_ms.get(1, 0.0) / all_ms,
                                          "single_conv_us_per_forward": kind_ms.get(1, 0.0) * 1e3 / passes,
                                          "what": "conv_pre + 4 upsamplers on stream_umma_kernel (conv_post rides the last fused launch)"}}
