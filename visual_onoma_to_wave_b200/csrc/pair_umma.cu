@@ -514,8 +514,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 o.w = pack_bf16x2(__uint_as_float(r[h * 8 + 6]), __uint_as_float(r[h * 8 + 7]));
                 o.x = lrelu_bf16x2(o.x, slope2); o.y = lrelu_bf16x2(o.y, slope2);
                 o.z = lrelu_bf16x2(o.z, slope2); o.w = lrelu_bf16x2(o.w, slope2);
-                if (!inside) o = make_uint4(0u, 0u, 0u, 0u);
-                st_shared_v4(t_row + (uint32_t)(((g * 4 + h) * NB * 128 + blk * 128) * 16), o);
+                // rows outside the utterance are conv2's zero padding: a predicated second store instead of four selects
+                const uint32_t addr = t_row + (uint32_t)(((g * 4 + h) * NB * 128 + blk * 128) * 16);
+                if (inside) st_shared_v4(addr, o);
+                else st_shared_v4(addr, make_uint4(0u, 0u, 0u, 0u));
             }
         };
         int n = 0;
@@ -702,13 +704,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_umma_kernel(const __grid
                 auto store_chunk = [&](const uint32_t (&r)[16], size_t e) {
                     float v[16];
 #pragma unroll
-                    for (int c = 0; c < 16; c += 2) {
+                    for (int c = 0; c < 16; c += 2) {      // scale = 1 in these launches (pair_launch): max(y, y * slope)
                         const float y0 = __uint_as_float(r[c]), y1 = __uint_as_float(r[c + 1]);
-                        float a0, a1, n0, n1;
-                        mul2(a0, a1, y0, y1, s_pos);
+                        float n0, n1;
                         mul2(n0, n1, y0, y1, s_neg);
-                        v[c] = fmaxf(a0, n0);
-                        v[c + 1] = fmaxf(a1, n1);
+                        v[c] = fmaxf(y0, n0);
+                        v[c + 1] = fmaxf(y1, n1);
                     }
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -1074,6 +1075,7 @@ int pair_launch(const PackedGroup& G, const PairIO& io, int B, int L, cudaStream
     }
     p.out_act = io.out_act;
     p.out_slope = io.out_slope; p.scale = io.scale;
+    if (io.scale != 1.0f) p.rinit = 0;            // the residual-initialised drain assumes scale = 1 (every ResBlock iteration)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(PAIR_THREADS);
