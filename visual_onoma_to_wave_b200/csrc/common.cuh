@@ -99,14 +99,19 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// suspendTimeHint of mbarrier.try_wait: the thread may stay suspended this long (it is woken when the phase completes).
+// Without it an attempt comes back after ~100 - 200 cycles, and the retry loops of the waiting roles -- epilogue warps
+// wait 50 - 90 % of a launch -- were a quarter of all instructions the fused kernel issued (ncu source page, C = 32, k = 3):
+// instructions that buy nothing and, at the board's power cap, cost clock.
+#define VO2W_MBAR_SUSPEND_NS 100000u
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(bar), "r"(parity)
+        : "r"(bar), "r"(parity), "r"(VO2W_MBAR_SUSPEND_NS)
         : "memory");
     return ok != 0;
 }
