@@ -1,4 +1,4 @@
-"""Short, deterministic target for ncu: N forwards of Generator at config 2 (B=16, T=172), bf16 mode."""
+"""Short, deterministic target for ncu: N forwards of Generator at T=172 (argv: N, B = 16, precision = bf16)."""
 import os
 import sys
 
@@ -10,8 +10,9 @@ from visual_onoma_to_wave_b200.synthetic import V1_CONFIG, seeded_state_dict, sy
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 16
+precision = sys.argv[3] if len(sys.argv) > 3 else "bf16"
 dev = torch.device("cuda:0")
-g = v.Generator(v.AttrDict(V1_CONFIG), precision="bf16")
+g = v.Generator(v.AttrDict(V1_CONFIG), precision=precision)
 g.eval()
 g.remove_weight_norm()
 g.load_state_dict(seeded_state_dict(1234))
