@@ -293,24 +293,37 @@ __global__ void __launch_bounds__(256) tf32_pack_kernel(const float* __restrict_
     packed[idx + 4 * (size_t)n_t] = lo;
 }
 
-// strided gather of a [Cout, Cin] matrix per (b, h) into the packed k = 1 stage layout; co fastest across threads
+// strided gather of a [Cout, Cin] matrix per (b, h) into the packed k = 1 stage layout.  One thread per (output row co,
+// chunk of T32_KC input channels), co fastest across threads: the four 16-byte stores of a thread (2 k-columns x hi / lo)
+// are each contiguous over the lanes of a warp (r * 4 floats), and the 8 source values of a thread are one 32-byte
+// sector when the input-channel axis is the contiguous one (keys: ld_ci = 1), or 8 loads each coalesced over co when
+// the output axis is (values, transposed while packing: ld_co = 1).
 __global__ void __launch_bounds__(256) tf32_pack_strided_kernel(const float* __restrict__ src, size_t bs, size_t hs, size_t ld_co,
                                                                 size_t ld_ci, int heads, int Cout, int Cin, int co_valid, int ci_valid,
                                                                 int n_t, float* __restrict__ packed) {
-    const int z = blockIdx.y;
+    const int z = blockIdx.y, chunks = Cin / T32_KC;
     const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (e >= (long long)Cout * Cin) return;
-    int co, ci;
-    if (ld_co <= ld_ci) { co = (int)(e % Cout); ci = (int)(e / Cout); }      // the contiguous source axis runs across threads
-    else { ci = (int)(e % Cin); co = (int)(e / Cin); }
-    float v = 0.f;
-    if (co < co_valid && ci < ci_valid) v = src[(size_t)(z / heads) * bs + (size_t)(z % heads) * hs + (size_t)co * ld_co + (size_t)ci * ld_ci];
-    const float hi = tf32_round(v), lo = tf32_round(v - hi);
-    const int tile = co / n_t, r = co % n_t, c = ci / T32_KC, kk = ci % T32_KC, chunks = Cin / T32_KC;
-    const size_t stage = (size_t)tile * chunks + c;
-    const size_t idx = (size_t)z * 2 * Cout * Cin + stage * (size_t)(16 * n_t) + (size_t)(kk >> 2) * (n_t * 8) + (size_t)r * 4 + (kk & 3);
-    packed[idx] = hi;
-    packed[idx + 4 * (size_t)n_t] = lo;
+    if (e >= (long long)Cout * chunks) return;
+    const int co = (int)(e % Cout), c = (int)(e / Cout);
+    const float* s = src + (size_t)(z / heads) * bs + (size_t)(z % heads) * hs + (size_t)co * ld_co + (size_t)c * T32_KC * ld_ci;
+    float v[T32_KC];
+#pragma unroll
+    for (int q = 0; q < T32_KC; ++q) {
+        v[q] = 0.f;
+        if (co < co_valid && c * T32_KC + q < ci_valid) v[q] = __ldg(s + (size_t)q * ld_ci);
+    }
+    const int tile = co / n_t, r = co % n_t;
+    float* o = packed + (size_t)z * 2 * Cout * Cin + ((size_t)tile * chunks + c) * (size_t)(16 * n_t) + (size_t)r * 4;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {                     // k-columns 0..3 and 4..7 of the chunk
+        float4 hi, lo;
+        hi.x = tf32_round(v[4 * h + 0]); lo.x = tf32_round(v[4 * h + 0] - hi.x);
+        hi.y = tf32_round(v[4 * h + 1]); lo.y = tf32_round(v[4 * h + 1] - hi.y);
+        hi.z = tf32_round(v[4 * h + 2]); lo.z = tf32_round(v[4 * h + 2] - hi.z);
+        hi.w = tf32_round(v[4 * h + 3]); lo.w = tf32_round(v[4 * h + 3] - hi.w);
+        *reinterpret_cast<float4*>(o + (size_t)h * (n_t * 8)) = hi;
+        *reinterpret_cast<float4*>(o + (size_t)h * (n_t * 8) + 4 * (size_t)n_t) = lo;
+    }
 }
 
 // output channels per CTA: 128 wherever it divides (2 row blocks x [main | small] x 128 = all 512 TMEM columns; the
@@ -367,7 +380,8 @@ int tf32_pack_strided(const float* src, size_t bs, size_t hs, size_t ld_co, size
                       int co_valid, int ci_valid, float* packed, cudaStream_t st) {
     VO2W_REQUIRE(tf32_conv_supported(Cout, Cin, 1) && B > 0 && heads > 0 && (long long)B * heads <= 65535,
                  "tf32 pack: shape Cout %d Cin %d unsupported", Cout, Cin);
-    dim3 grid((unsigned)vo2w_ceil_div((long long)Cout * Cin, 256), (unsigned)(B * heads));
+    VO2W_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0, "tf32 pack: the packed operand must be 16-byte aligned");
+    dim3 grid((unsigned)vo2w_ceil_div((long long)Cout * (Cin / T32_KC), 256), (unsigned)(B * heads));
     tf32_pack_strided_kernel<<<grid, 256, 0, st>>>(src, bs, hs, ld_co, ld_ci, heads, Cout, Cin, co_valid, ci_valid, tile_width(Cout, 1),
                                                    packed);
     VO2W_CUDA_OK(cudaGetLastError());

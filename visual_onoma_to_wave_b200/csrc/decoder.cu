@@ -170,7 +170,10 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const float* __rest
 }
 
 // in place: S[r, 0..Lp) -> softmax(S[r, :] * scale) over the valid keys (j < L and not padding), zeros elsewhere
-// (attn / temperature, masked_fill(mask, -inf), Softmax(dim=2): Modules.py:15-22).  rows r = (b, l, h); one warp per row.
+// (attn / temperature, masked_fill(mask, -inf), Softmax(dim=2): Modules.py:15-22).  rows r = (b, l, h); one warp per row,
+// the row in registers: MAXP values per lane (Lp <= 32 * MAXP), instantiated for 8 / 16 / 32 so that a 512-key row does
+// not pay for 1 024 (the results do not depend on MAXP: the extra slots hold -inf and are never summed).
+template <int MAXP>
 __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S, const uint8_t* __restrict__ mask, long long rows,
                                                            int L, int Lp, int rows_per_b, float scale) {
     const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -178,7 +181,6 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S
     const int lane = threadIdx.x & 31;
     float* row = S + (size_t)r * Lp;
     const uint8_t* mb = mask ? mask + (size_t)(r / rows_per_b) * L : nullptr;
-    constexpr int MAXP = 32;                          // Lp <= 1024 per pass in registers
     float v[MAXP];
     float mx = -INFINITY;
 #pragma unroll
@@ -253,8 +255,14 @@ int rows_attention_gemm(const float* qkv, const uint8_t* mask, float* out, int B
     qk.ldx = (int)row3; qk.x_hs = AD; qk.ldo = n_head * Lp; qk.o_hs = Lp; qk.heads = n_head; qk.w_zs = (size_t)2 * Lp * AD;
     if ((rc = tf32_conv1d(qk, st)) != VO2W_OK) return rc;
     const long long rows = (long long)B * L * n_head;
-    if (Lp <= 1024)      // the row fits one warp's registers: one pass
-        softmax_rows_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
+    const unsigned sgrid = (unsigned)vo2w_ceil_div(rows, 8);
+    const float sscale = 1.0f / sqrtf((float)AD);
+    if (Lp <= 256)       // the row fits one warp's registers: one pass
+        softmax_rows_kernel<8><<<sgrid, 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, sscale);
+    else if (Lp <= 512)
+        softmax_rows_kernel<16><<<sgrid, 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, sscale);
+    else if (Lp <= 1024)
+        softmax_rows_kernel<32><<<sgrid, 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, sscale);
     else
         softmax_rows_long_kernel<<<(unsigned)vo2w_ceil_div(rows, 8), 256, 0, st>>>(S, mask, rows, L, Lp, L * n_head, 1.0f / sqrtf((float)AD));
     VO2W_CUDA_OK(cudaGetLastError());
